@@ -1,0 +1,357 @@
+/*
+ * TEST INFRASTRUCTURE ONLY -- the CPU oracle for the sample -> unique/remap -> extract path.
+ *
+ * A plain-C restatement of the reference's algorithms, one function per reference routine, each
+ * citing the reference file:line it follows (paths relative to /root/reference/samgraph/common).
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg may load this library, and
+ * only as the checker.  The product (xgnn_b200/) never links, loads or calls anything in here.
+ *
+ * Pinning status (see DESIGN.md "Oracle"):
+ *   - khop0 (deg <= fanout branch), hashtable0, map_edges, extract: pinned against the reference's
+ *     own CPU code compiled in place (oracle/_ref/libxgnn_ref.so) by tests/test_oracle_vs_ref.py and
+ *     against committed fixtures generated from it (tests/golden/*.npz).
+ *   - hashtable properties: pinned against the reference's gtest vectors
+ *     (samgraph/unittest/test_hashmap.cc:98-172).
+ *   - khop0 deg > fanout, khop1/weighted/random-walk: distribution is the contract (the reference
+ *     seeds from the wall clock / a default-seeded thread_local mt19937), so only the law is pinned.
+ *   - routing / partition layout / miss-cache split: no reference test exists ("parity unpinned by
+ *     the reference's tests"); restated from the cited lines.
+ */
+#include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
+#include <stddef.h>
+#include <math.h>
+
+#define ORC_EMPTY 0xFFFFFFFFu /* Constant::kEmptyKey, constant.h:75 */
+
+/* ------------------------------------------------------------------------------------------ */
+/* Small deterministic RNG for the oracle's random branches (splitmix64).  The reference uses a
+ * default-seeded thread_local std::mt19937 (cpu/cpu_random.cc:26-30); only uniformity matters. */
+static inline uint64_t orc_mix(uint64_t *s) {
+  uint64_t z = (*s += 0x9E3779B97F4A7C15ull);
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+/* uniform integer in [0, n) without modulo bias */
+static inline uint64_t orc_below(uint64_t *s, uint64_t n) {
+  uint64_t lim = UINT64_MAX - (UINT64_MAX % n);
+  uint64_t r;
+  do { r = orc_mix(s); } while (r >= lim);
+  return r % n;
+}
+
+/* stable removal of ORC_EMPTY entries; returns the kept count (std::remove_if in
+ * cpu/cpu_sampling_khop0.cc:70-76) */
+static size_t orc_compact(uint32_t *a, size_t n) {
+  size_t w = 0;
+  for (size_t i = 0; i < n; ++i)
+    if (a[i] != ORC_EMPTY) a[w++] = a[i];
+  return w;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* KHop0: cpu/cpu_sampling_khop0.cc:29-83 (GPU twin cuda/cuda_sampling_khop0.cu:102-153).
+ * For every input node: degree <= fanout -> all neighbours in CSR order; otherwise Algorithm-R
+ * reservoir of size fanout.  Slots are node-major / slot-minor, padding removed stably.
+ * out_src/out_dst must hold num_input*fanout entries. */
+size_t orc_sample_khop0(const uint32_t *indptr, const uint32_t *indices, const uint32_t *input,
+                        size_t num_input, size_t fanout, uint32_t *out_src, uint32_t *out_dst,
+                        uint64_t seed) {
+  for (size_t i = 0; i < num_input; ++i) {
+    const uint32_t v = input[i];
+    const uint32_t begin = indptr[v];
+    const uint32_t deg = indptr[v + 1] - begin;
+    uint32_t *src = out_src + i * fanout;
+    uint32_t *dst = out_dst + i * fanout;
+    if (deg <= fanout) {
+      for (size_t j = 0; j < fanout; ++j) {
+        src[j] = j < deg ? v : ORC_EMPTY;
+        dst[j] = j < deg ? indices[begin + j] : ORC_EMPTY;
+      }
+    } else {
+      uint64_t s = seed ^ (0xD1B54A32D192ED03ull * (i + 1));
+      for (size_t j = 0; j < fanout; ++j) {
+        src[j] = v;
+        dst[j] = indices[begin + j];
+      }
+      for (size_t j = fanout; j < deg; ++j) {
+        uint64_t k = orc_below(&s, j + 1); /* RandomID(0, j+1) is inclusive [0, j+1]: see note */
+        if (k < fanout) dst[k] = indices[begin + j];
+      }
+    }
+  }
+  size_t n = orc_compact(out_src, num_input * fanout);
+  orc_compact(out_dst, num_input * fanout);
+  return n;
+}
+/* Note on the reservoir: the reference draws RandomID(0, j+1) with an *inclusive*
+ * std::uniform_int_distribution (cpu/cpu_random.cc:27-29), i.e. k in [0, j+1] -- one value too
+ * many, which biases late elements slightly low.  The stated contract (BASELINE.json north_star;
+ * SURVEY.md section 9 item 12) is the uniform without-replacement law, so the oracle uses the
+ * textbook k in [0, j]. */
+
+/* per-node output count min(deg, fanout): the size law shared by KHop0/2/3. */
+void orc_sample_counts(const uint32_t *indptr, const uint32_t *input, size_t num_input,
+                       size_t fanout, uint32_t *counts) {
+  for (size_t i = 0; i < num_input; ++i) {
+    uint32_t deg = indptr[input[i] + 1] - indptr[input[i]];
+    counts[i] = deg < fanout ? deg : (uint32_t)fanout;
+  }
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* Ordered hash table, first-occurrence numbering: cpu/cpu_hashtable0.cc:37-66.  This is also one
+ * legal outcome of the GPU table (cuda/cuda_hashtable.cu:744-912), whose winner among duplicate
+ * occurrences is racy; it is the only deterministic one. */
+typedef struct {
+  uint32_t *keys;   /* open addressing, ORC_EMPTY = free */
+  uint32_t *vals;   /* local id */
+  uint32_t *n2o;    /* local id -> global id */
+  size_t cap;       /* power of two */
+  size_t n2o_cap;
+  size_t num_items;
+} orc_table;
+
+static size_t orc_pow2(size_t n) { size_t c = 16; while (c < n) c <<= 1; return c; }
+static inline size_t orc_hash(uint32_t k, size_t mask) {
+  uint32_t h = k * 0x9E3779B1u;
+  return (h ^ (h >> 15)) & mask;
+}
+
+orc_table *orc_table_create(size_t max_items) {
+  orc_table *t = (orc_table *)calloc(1, sizeof(orc_table));
+  t->cap = orc_pow2(max_items * 2 + 16);
+  t->n2o_cap = max_items + 16;
+  t->keys = (uint32_t *)malloc(t->cap * sizeof(uint32_t));
+  t->vals = (uint32_t *)malloc(t->cap * sizeof(uint32_t));
+  t->n2o = (uint32_t *)malloc(t->n2o_cap * sizeof(uint32_t));
+  memset(t->keys, 0xFF, t->cap * sizeof(uint32_t));
+  return t;
+}
+void orc_table_destroy(orc_table *t) {
+  if (!t) return;
+  free(t->keys); free(t->vals); free(t->n2o); free(t);
+}
+/* cpu_hashtable0.cc:61-64 */
+void orc_table_reset(orc_table *t) {
+  memset(t->keys, 0xFF, t->cap * sizeof(uint32_t));
+  t->num_items = 0;
+}
+size_t orc_table_num_items(const orc_table *t) { return t->num_items; }
+
+static int orc_table_find(const orc_table *t, uint32_t key, uint32_t *val) {
+  size_t mask = t->cap - 1, p = orc_hash(key, mask);
+  while (t->keys[p] != ORC_EMPTY) {
+    if (t->keys[p] == key) { *val = t->vals[p]; return 1; }
+    p = (p + 1) & mask;
+  }
+  return 0;
+}
+/* cpu_hashtable0.cc:37-47 : sequential insert, a new key gets id = num_items++ */
+int orc_table_populate(orc_table *t, const uint32_t *input, size_t n) {
+  size_t mask = t->cap - 1;
+  for (size_t i = 0; i < n; ++i) {
+    uint32_t key = input[i];
+    size_t p = orc_hash(key, mask);
+    int found = 0;
+    while (t->keys[p] != ORC_EMPTY) {
+      if (t->keys[p] == key) { found = 1; break; }
+      p = (p + 1) & mask;
+    }
+    if (!found) {
+      if (t->num_items >= t->n2o_cap) return -1;
+      t->keys[p] = key;
+      t->vals[p] = (uint32_t)t->num_items;
+      t->n2o[t->num_items++] = key;
+    }
+  }
+  return 0;
+}
+/* cpu_hashtable0.cc:49-51 */
+void orc_table_map_nodes(const orc_table *t, uint32_t *out, size_t n) {
+  memcpy(out, t->n2o, n * sizeof(uint32_t));
+}
+/* cpu_hashtable0.cc:53-66 and cuda/cuda_mapping.cu:50-80 ; returns -1 when a key is absent
+ * (the reference CHECK-aborts) */
+int orc_table_map_edges(const orc_table *t, const uint32_t *src, const uint32_t *dst, size_t len,
+                        uint32_t *new_src, uint32_t *new_dst) {
+  for (size_t i = 0; i < len; ++i) {
+    if (!orc_table_find(t, src[i], &new_src[i])) return -1;
+    if (!orc_table_find(t, dst[i], &new_dst[i])) return -1;
+  }
+  return 0;
+}
+/* DeviceOrderedHashTable::SearchO2N(id)->local, cuda/cuda_hashtable.h:57-60; ORC_EMPTY if absent */
+void orc_table_lookup(const orc_table *t, const uint32_t *keys, size_t n, uint32_t *local) {
+  for (size_t i = 0; i < n; ++i)
+    if (!orc_table_find(t, keys[i], &local[i])) local[i] = ORC_EMPTY;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* Row gather: cpu/cpu_extraction.cc:31-45,66-90 and cuda/cuda_extraction.cu:31-49.  A byte copy for
+ * every dtype, so it is stated on row_bytes = dim * sizeof(T). */
+void orc_extract(void *dst, const void *src, const uint32_t *index, size_t num_index,
+                 size_t row_bytes) {
+#pragma omp parallel for schedule(static)
+  for (size_t i = 0; i < num_index; ++i)
+    memcpy((char *)dst + i * row_bytes, (const char *)src + (size_t)index[i] * row_bytes, row_bytes);
+}
+/* mock variant: cpu/cpu_extraction.cc:47-62 -- the *row index* is masked to 2^k rows */
+void orc_mock_extract(void *dst, const void *src, const uint32_t *index, size_t num_index,
+                      size_t row_bytes, unsigned empty_feat_bits) {
+  size_t mask = ((size_t)1 << empty_feat_bits) - 1;
+  for (size_t i = 0; i < num_index; ++i)
+    memcpy((char *)dst + i * row_bytes, (const char *)src + ((size_t)index[i] & mask) * row_bytes,
+           row_bytes);
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* GGMS topology routing: DeviceDistGraph::_GetRealPartId, cuda/dist_graph.h:141-151.
+ * part == num_part means "host whole-graph slot". */
+void orc_route_node(uint32_t v, uint32_t num_part, uint32_t num_cache_node, uint32_t *part,
+                    uint32_t *row) {
+  if (v < num_cache_node) { *part = v % num_part; *row = v / num_part; }
+  else { *part = num_part; *row = v; }
+}
+/* num_cache_node: smallest n with indptr[n] >= floor(E * ratio), dist/dist_engine.cc:223-232 */
+uint32_t orc_num_cache_node(const uint32_t *indptr, uint32_t num_node, double ratio) {
+  uint64_t want = (uint64_t)((double)indptr[num_node] * ratio);
+  uint32_t n = 0;
+  while (n < num_node && indptr[n] < want) ++n;
+  return n;
+}
+/* partition p's CSR, rebased to 0: DistGraph::_DatasetPartition, cuda/dist_graph.cu:228-272.
+ * Sizes: indptr has ceil((n-p)/P)+1 entries.  Call with part_indices==NULL to size. Returns the
+ * partition's edge count; *indptr_len receives the indptr length. */
+size_t orc_partition_csr(const uint32_t *indptr, const uint32_t *indices, uint32_t num_cache_node,
+                         uint32_t part, uint32_t num_part, uint32_t *part_indptr,
+                         uint32_t *part_indices, size_t *indptr_len) {
+  size_t rows = num_cache_node / num_part + (part < num_cache_node % num_part ? 1 : 0);
+  size_t e = 0, r = 0;
+  for (uint32_t v = part; v < num_cache_node; v += num_part, ++r) {
+    uint32_t deg = indptr[v + 1] - indptr[v];
+    if (part_indptr) part_indptr[r] = (uint32_t)e;
+    if (part_indices) memcpy(part_indices + e, indices + indptr[v], deg * sizeof(uint32_t));
+    e += deg;
+  }
+  if (part_indptr) part_indptr[rows] = (uint32_t)e;
+  if (indptr_len) *indptr_len = rows + 1;
+  return e;
+}
+/* KHop0 over a partitioned topology: same law as orc_sample_khop0 but every neighbour list is
+ * reached through the routing above (cuda_sampling_khop0.cu:119-121 with GraphType =
+ * DeviceDistGraph).  part_indptr/part_indices have num_part+1 entries, the last being the whole
+ * host graph.  Used to prove the partitioned store returns the same lists as the flat CSR. */
+size_t orc_sample_khop0_dist(const uint32_t *const *part_indptr, const uint32_t *const *part_indices,
+                             uint32_t num_part, uint32_t num_cache_node, const uint32_t *input,
+                             size_t num_input, size_t fanout, uint32_t *out_src, uint32_t *out_dst,
+                             uint64_t seed) {
+  for (size_t i = 0; i < num_input; ++i) {
+    uint32_t v = input[i], part, row;
+    orc_route_node(v, num_part, num_cache_node, &part, &row);
+    const uint32_t begin = part_indptr[part][row];
+    const uint32_t deg = part_indptr[part][row + 1] - begin;
+    const uint32_t *edges = part_indices[part] + begin;
+    uint32_t *src = out_src + i * fanout, *dst = out_dst + i * fanout;
+    if (deg <= fanout) {
+      for (size_t j = 0; j < fanout; ++j) {
+        src[j] = j < deg ? v : ORC_EMPTY;
+        dst[j] = j < deg ? edges[j] : ORC_EMPTY;
+      }
+    } else {
+      uint64_t s = seed ^ (0xD1B54A32D192ED03ull * (i + 1));
+      for (size_t j = 0; j < fanout; ++j) { src[j] = v; dst[j] = edges[j]; }
+      for (size_t j = fanout; j < deg; ++j) {
+        uint64_t k = orc_below(&s, j + 1);
+        if (k < fanout) dst[k] = edges[j];
+      }
+    }
+  }
+  size_t n = orc_compact(out_src, num_input * fanout);
+  orc_compact(out_dst, num_input * fanout);
+  return n;
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* Feature cache: direct-address table node -> cache rank (cuda/cuda_cache_manager_host.cc:197-229)
+ * rank_nodes[0..num_cached) is the (already shuffled) cached prefix of the policy's rank list. */
+void orc_build_cache_table(const uint32_t *rank_nodes, size_t num_cached, uint32_t *table,
+                           size_t num_node) {
+  for (size_t i = 0; i < num_node; ++i) table[i] = ORC_EMPTY;
+  for (size_t i = 0; i < num_cached; ++i) table[rank_nodes[i]] = (uint32_t)i;
+}
+/* stable split of the batch into misses (src = node id) and hits (src = cache rank), dst = position
+ * in the batch: GPUCacheManager::GetMissCacheIndex, cuda/cuda_cache_manager_device.cu:41-169,355-441 */
+void orc_miss_cache_index(const uint32_t *table, const uint32_t *nodes, size_t n,
+                          uint32_t *miss_src, uint32_t *miss_dst, size_t *num_miss,
+                          uint32_t *cache_src, uint32_t *cache_dst, size_t *num_cache) {
+  size_t m = 0, c = 0;
+  for (size_t i = 0; i < n; ++i) {
+    uint32_t r = table[nodes[i]];
+    if (r == ORC_EMPTY) { miss_src[m] = nodes[i]; miss_dst[m++] = (uint32_t)i; }
+    else { cache_src[c] = r; cache_dst[c++] = (uint32_t)i; }
+  }
+  *num_miss = m; *num_cache = c;
+}
+/* rows of partition p of the feature cache: rank r -> part r%P, row r/P
+ * (cuda/dist_graph.cu:493-505, cuda/dist_graph.h:203-207).  Returns number of rows. */
+size_t orc_partition_features(const void *feat, size_t row_bytes, const uint32_t *rank_nodes,
+                              size_t num_cached, uint32_t part, uint32_t num_part, void *out) {
+  size_t r = 0;
+  for (size_t i = part; i < num_cached; i += num_part, ++r)
+    if (out) memcpy((char *)out + r * row_bytes, (const char *)feat + (size_t)rank_nodes[i] * row_bytes,
+                    row_bytes);
+  return r;
+}
+/* miss rows from the host table, hit rows from the partitioned cache:
+ * extract_miss_data + combine_cache_data_for_partition, cuda_cache_manager_device.cu:234-299 */
+void orc_extract_ggms(void *out, size_t row_bytes, const uint32_t *nodes, size_t n,
+                      const uint32_t *table, const void *host_feat, const void *const *part_feat,
+                      uint32_t num_part) {
+  for (size_t i = 0; i < n; ++i) {
+    uint32_t r = table ? table[nodes[i]] : ORC_EMPTY;
+    const char *src = r == ORC_EMPTY
+                          ? (const char *)host_feat + (size_t)nodes[i] * row_bytes
+                          : (const char *)part_feat[r % num_part] + (size_t)(r / num_part) * row_bytes;
+    memcpy((char *)out + i * row_bytes, src, row_bytes);
+  }
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* One minibatch, the call order of DoCPUSample (cpu/cpu_loops.cc:55-192) == dist::DoGPUSample
+ * (dist/dist_loops.cc:62-368): table reset, seeds inserted, then layers last -> first:
+ * sample, insert out_dst, unique list (previous input is its prefix), remap (src,dst).
+ * Layer l outputs: row[l] = local(out_dst) (neighbour), col[l] = local(out_src) (seed side),
+ * counts[3l..3l+2] = {num_src = num_unique, num_dst = num_input, num_edge}.
+ * Buffers row[l]/col[l] must hold PredictNumNodes-style worst case; pass scratch of the same size.
+ * Returns |input_nodes| (written to input_nodes). */
+size_t orc_minibatch(const uint32_t *indptr, const uint32_t *indices, const uint32_t *seeds,
+                     size_t num_seeds, const size_t *fanouts, int num_layers, uint64_t seed,
+                     uint32_t **row, uint32_t **col, size_t *counts, uint32_t *input_nodes,
+                     size_t max_nodes) {
+  orc_table *t = orc_table_create(max_nodes);
+  orc_table_populate(t, seeds, num_seeds);
+  uint32_t *cur = (uint32_t *)malloc(max_nodes * sizeof(uint32_t));
+  memcpy(cur, seeds, num_seeds * sizeof(uint32_t));
+  size_t num_input = num_seeds;
+  for (int l = num_layers - 1; l >= 0; --l) {
+    size_t f = fanouts[l];
+    uint32_t *src = (uint32_t *)malloc((num_input * f + 1) * sizeof(uint32_t));
+    uint32_t *dst = (uint32_t *)malloc((num_input * f + 1) * sizeof(uint32_t));
+    size_t e = orc_sample_khop0(indptr, indices, cur, num_input, f, src, dst,
+                                seed + 0x1000003ull * (uint64_t)l);
+    orc_table_populate(t, dst, e);
+    size_t u = orc_table_num_items(t);
+    orc_table_map_edges(t, src, dst, e, col[l], row[l]);
+    counts[3 * l + 0] = u; counts[3 * l + 1] = num_input; counts[3 * l + 2] = e;
+    orc_table_map_nodes(t, cur, u);
+    num_input = u;
+    free(src); free(dst);
+  }
+  memcpy(input_nodes, cur, num_input * sizeof(uint32_t));
+  free(cur);
+  orc_table_destroy(t);
+  return num_input;
+}

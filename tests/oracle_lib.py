@@ -1,0 +1,270 @@
+"""ctypes access to the CPU oracle (oracle/liboracle.so) and, when prebuilt, to the reference's own
+CPU code (oracle/_ref/libxgnn_ref.so).  TEST INFRASTRUCTURE -- never imported by xgnn_b200/."""
+from __future__ import annotations
+
+import ctypes
+from ctypes import POINTER, c_double, c_int, c_size_t, c_uint32, c_uint64, c_void_p
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent.parent
+ORACLE_SO = ROOT / "oracle" / "liboracle.so"
+REF_SO = ROOT / "oracle" / "_ref" / "libxgnn_ref.so"
+EMPTY = 0xFFFFFFFF
+
+orc = ctypes.CDLL(str(ORACLE_SO))
+ref = ctypes.CDLL(str(REF_SO)) if REF_SO.exists() else None
+
+u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+
+
+def _sig(lib, name, restype, *args):
+    fn = getattr(lib, name)
+    fn.restype = restype
+    fn.argtypes = list(args)
+
+
+_sig(orc, "orc_sample_khop0", c_size_t, u32p, u32p, u32p, c_size_t, c_size_t, u32p, u32p, c_uint64)
+_sig(orc, "orc_sample_counts", None, u32p, u32p, c_size_t, c_size_t, u32p)
+_sig(orc, "orc_table_create", c_void_p, c_size_t)
+_sig(orc, "orc_table_destroy", None, c_void_p)
+_sig(orc, "orc_table_reset", None, c_void_p)
+_sig(orc, "orc_table_num_items", c_size_t, c_void_p)
+_sig(orc, "orc_table_populate", c_int, c_void_p, u32p, c_size_t)
+_sig(orc, "orc_table_map_nodes", None, c_void_p, u32p, c_size_t)
+_sig(orc, "orc_table_map_edges", c_int, c_void_p, u32p, u32p, c_size_t, u32p, u32p)
+_sig(orc, "orc_table_lookup", None, c_void_p, u32p, c_size_t, u32p)
+_sig(orc, "orc_extract", None, c_void_p, c_void_p, u32p, c_size_t, c_size_t)
+_sig(orc, "orc_mock_extract", None, c_void_p, c_void_p, u32p, c_size_t, c_size_t, ctypes.c_uint)
+_sig(orc, "orc_route_node", None, c_uint32, c_uint32, c_uint32, POINTER(c_uint32), POINTER(c_uint32))
+_sig(orc, "orc_num_cache_node", c_uint32, u32p, c_uint32, c_double)
+_sig(orc, "orc_partition_csr", c_size_t, u32p, u32p, c_uint32, c_uint32, c_uint32, c_void_p, c_void_p,
+     POINTER(c_size_t))
+_sig(orc, "orc_build_cache_table", None, u32p, c_size_t, u32p, c_size_t)
+_sig(orc, "orc_miss_cache_index", None, u32p, u32p, c_size_t, u32p, u32p, POINTER(c_size_t), u32p, u32p,
+     POINTER(c_size_t))
+_sig(orc, "orc_partition_features", c_size_t, c_void_p, c_size_t, u32p, c_size_t, c_uint32, c_uint32, c_void_p)
+_sig(orc, "orc_extract_ggms", None, c_void_p, c_size_t, u32p, c_size_t, c_void_p, c_void_p, c_void_p, c_uint32)
+
+
+def u32(a) -> np.ndarray:
+    return np.ascontiguousarray(np.asarray(a).astype(np.uint32, copy=False))
+
+
+# ---- oracle wrappers --------------------------------------------------------------------------
+def sample_khop0(indptr, indices, inp, fanout, seed=1):
+    inp = u32(inp)
+    src = np.empty(max(len(inp) * fanout, 1), np.uint32)
+    dst = np.empty(max(len(inp) * fanout, 1), np.uint32)
+    n = orc.orc_sample_khop0(u32(indptr), u32(indices), inp, len(inp), fanout, src, dst, seed)
+    return src[:n].copy(), dst[:n].copy()
+
+
+class Table:
+    """CPUHashTable0 restatement (first-occurrence ids)."""
+
+    def __init__(self, max_items):
+        self.h = orc.orc_table_create(max_items)
+
+    def __del__(self):
+        orc.orc_table_destroy(self.h)
+
+    def reset(self):
+        orc.orc_table_reset(self.h)
+
+    def populate(self, a):
+        a = u32(a)
+        assert orc.orc_table_populate(self.h, a, len(a)) == 0
+
+    def num_items(self):
+        return orc.orc_table_num_items(self.h)
+
+    def unique(self):
+        out = np.empty(max(self.num_items(), 1), np.uint32)
+        orc.orc_table_map_nodes(self.h, out, self.num_items())
+        return out[: self.num_items()]
+
+    def map_edges(self, src, dst):
+        src, dst = u32(src), u32(dst)
+        ns, nd = np.empty(max(len(src), 1), np.uint32), np.empty(max(len(src), 1), np.uint32)
+        assert orc.orc_table_map_edges(self.h, src, dst, len(src), ns, nd) == 0
+        return ns[: len(src)], nd[: len(src)]
+
+    def lookup(self, keys):
+        keys = u32(keys)
+        out = np.empty(max(len(keys), 1), np.uint32)
+        orc.orc_table_lookup(self.h, keys, len(keys), out)
+        return out[: len(keys)]
+
+
+def extract(src: np.ndarray, index) -> np.ndarray:
+    index = u32(index)
+    src = np.ascontiguousarray(src)
+    row_bytes = src.strides[0] if src.ndim == 2 else src.itemsize
+    out = np.empty((len(index),) + src.shape[1:], src.dtype)
+    orc.orc_extract(out.ctypes.data, src.ctypes.data, index, len(index), row_bytes)
+    return out
+
+
+def route_node(v, num_part, num_cache_node):
+    p, r = c_uint32(), c_uint32()
+    orc.orc_route_node(v, num_part, num_cache_node, ctypes.byref(p), ctypes.byref(r))
+    return p.value, r.value
+
+
+def num_cache_node(indptr, ratio):
+    indptr = u32(indptr)
+    return orc.orc_num_cache_node(indptr, len(indptr) - 1, ratio)
+
+
+def partition_csr(indptr, indices, ncn, part, num_part):
+    indptr, indices = u32(indptr), u32(indices)
+    ln = c_size_t()
+    e = orc.orc_partition_csr(indptr, indices, ncn, part, num_part, None, None, ctypes.byref(ln))
+    pi = np.zeros(ln.value, np.uint32)
+    px = np.zeros(max(e, 1), np.uint32)
+    orc.orc_partition_csr(indptr, indices, ncn, part, num_part, pi.ctypes.data, px.ctypes.data, ctypes.byref(ln))
+    return pi, px[:e]
+
+
+def build_cache_table(rank_nodes, num_cached, num_node):
+    t = np.empty(num_node, np.uint32)
+    orc.orc_build_cache_table(u32(rank_nodes), num_cached, t, num_node)
+    return t
+
+
+def miss_cache_index(table, nodes):
+    nodes = u32(nodes)
+    n = len(nodes)
+    bufs = [np.empty(max(n, 1), np.uint32) for _ in range(4)]
+    nm, nc = c_size_t(), c_size_t()
+    orc.orc_miss_cache_index(u32(table), nodes, n, bufs[0], bufs[1], ctypes.byref(nm), bufs[2], bufs[3],
+                             ctypes.byref(nc))
+    return bufs[0][: nm.value], bufs[1][: nm.value], bufs[2][: nc.value], bufs[3][: nc.value]
+
+
+def partition_features(feat, rank_nodes, num_cached, part, num_part):
+    feat = np.ascontiguousarray(feat)
+    rb = feat.strides[0]
+    rows = orc.orc_partition_features(feat.ctypes.data, rb, u32(rank_nodes), num_cached, part, num_part, None)
+    out = np.empty((max(rows, 1),) + feat.shape[1:], feat.dtype)
+    orc.orc_partition_features(feat.ctypes.data, rb, u32(rank_nodes), num_cached, part, num_part, out.ctypes.data)
+    return out[:rows]
+
+
+def extract_ggms(feat, nodes, table, parts):
+    feat = np.ascontiguousarray(feat)
+    nodes = u32(nodes)
+    rb = feat.strides[0]
+    out = np.empty((len(nodes),) + feat.shape[1:], feat.dtype)
+    arr = (c_void_p * max(len(parts), 1))(*[p.ctypes.data for p in parts])
+    orc.orc_extract_ggms(out.ctypes.data, rb, nodes, len(nodes), u32(table).ctypes.data if table is not None else None,
+                         feat.ctypes.data, arr, len(parts))
+    return out
+
+
+_sig(orc, "orc_minibatch", c_size_t, u32p, u32p, u32p, c_size_t, POINTER(c_size_t), c_int, c_uint64,
+     POINTER(c_void_p), POINTER(c_void_p), POINTER(c_size_t), u32p, c_size_t)
+
+
+def predict_num_nodes(batch, fanouts):
+    """PredictNumNodes, common.cc:488-497: worst-case |input_nodes| of a batch (fanouts consumed last -> first)."""
+    cur, total = batch, batch
+    for f in reversed(list(fanouts)):
+        cur = cur * f
+        total += cur
+    return total
+
+
+def minibatch(indptr, indices, seeds, fanouts, seed=1):
+    """DoCPUSample call order (cpu/cpu_loops.cc:55-192) on the oracle's table + khop0."""
+    seeds = u32(seeds)
+    L = len(fanouts)
+    max_nodes = min(predict_num_nodes(len(seeds), fanouts), len(indptr) - 1 + len(seeds)) + 16
+    # worst-case edges per layer
+    caps, cur = [0] * L, len(seeds)
+    for l in range(L - 1, -1, -1):
+        caps[l] = cur * fanouts[l] + 1
+        cur = min(cur + caps[l], max_nodes)
+    rows = [np.empty(c, np.uint32) for c in caps]
+    cols = [np.empty(c, np.uint32) for c in caps]
+    rp = (c_void_p * L)(*[r.ctypes.data for r in rows])
+    cp = (c_void_p * L)(*[c.ctypes.data for c in cols])
+    counts = (c_size_t * (3 * L))()
+    fan = (c_size_t * L)(*fanouts)
+    inp = np.empty(max_nodes, np.uint32)
+    n = orc.orc_minibatch(u32(indptr), u32(indices), seeds, len(seeds), fan, L, seed, rp, cp, counts, inp, max_nodes)
+    return {
+        "row": [rows[l][: counts[3 * l + 2]].copy() for l in range(L)],
+        "col": [cols[l][: counts[3 * l + 2]].copy() for l in range(L)],
+        "num_src": [counts[3 * l] for l in range(L)],
+        "num_dst": [counts[3 * l + 1] for l in range(L)],
+        "num_edge": [counts[3 * l + 2] for l in range(L)],
+        "input_nodes": inp[:n].copy(),
+    }
+
+
+# ---- reference (oracle/_ref) wrappers -----------------------------------------------------------
+if ref is not None:
+    _sig(ref, "ref_set_threads", None, c_int)
+    _sig(ref, "ref_cpu_sample_khop0", None, u32p, u32p, u32p, c_size_t, u32p, u32p, POINTER(c_size_t), c_size_t)
+    _sig(ref, "ref_cpu_extract", None, c_void_p, c_void_p, u32p, c_size_t, c_size_t, c_int)
+    _sig(ref, "ref_hashtable_create", c_void_p, c_int, c_size_t)
+    _sig(ref, "ref_hashtable_destroy", None, c_void_p)
+    _sig(ref, "ref_hashtable_reset", None, c_void_p)
+    _sig(ref, "ref_hashtable_populate", None, c_void_p, u32p, c_size_t)
+    _sig(ref, "ref_hashtable_num_items", c_size_t, c_void_p)
+    _sig(ref, "ref_hashtable_map_nodes", None, c_void_p, u32p, c_size_t)
+    _sig(ref, "ref_hashtable_map_edges", None, c_void_p, u32p, u32p, c_size_t, u32p, u32p)
+    for _n in ("f32", "f16", "i64", "u8", "i32", "f64"):
+        _sig(ref, f"ref_dtype_{_n}", c_int)
+    ref.ref_set_threads(4)
+
+    REF_DTYPE = {np.dtype(np.float32): ref.ref_dtype_f32(), np.dtype(np.float16): ref.ref_dtype_f16(),
+                 np.dtype(np.int64): ref.ref_dtype_i64(), np.dtype(np.uint8): ref.ref_dtype_u8(),
+                 np.dtype(np.int32): ref.ref_dtype_i32(), np.dtype(np.float64): ref.ref_dtype_f64()}
+
+    def ref_sample_khop0(indptr, indices, inp, fanout):
+        inp = u32(inp)
+        src = np.empty(max(len(inp) * fanout, 1), np.uint32)
+        dst = np.empty(max(len(inp) * fanout, 1), np.uint32)
+        n = c_size_t()
+        ref.ref_cpu_sample_khop0(u32(indptr), u32(indices), inp, len(inp), src, dst, ctypes.byref(n), fanout)
+        return src[: n.value].copy(), dst[: n.value].copy()
+
+    def ref_extract(src: np.ndarray, index):
+        index = u32(index)
+        src = np.ascontiguousarray(src)
+        dim = src.shape[1] if src.ndim == 2 else 1
+        out = np.empty((len(index),) + src.shape[1:], src.dtype)
+        ref.ref_cpu_extract(out.ctypes.data, src.ctypes.data, index, len(index), dim, REF_DTYPE[src.dtype])
+        return out
+
+    class RefTable:
+        def __init__(self, kind, max_items):
+            self.h = ref.ref_hashtable_create(kind, max_items)
+
+        def __del__(self):
+            ref.ref_hashtable_destroy(self.h)
+
+        def reset(self):
+            ref.ref_hashtable_reset(self.h)
+
+        def populate(self, a):
+            a = u32(a)
+            ref.ref_hashtable_populate(self.h, a, len(a))
+
+        def num_items(self):
+            return ref.ref_hashtable_num_items(self.h)
+
+        def unique(self):
+            out = np.empty(max(self.num_items(), 1), np.uint32)
+            ref.ref_hashtable_map_nodes(self.h, out, self.num_items())
+            return out[: self.num_items()]
+
+        def map_edges(self, src, dst):
+            src, dst = u32(src), u32(dst)
+            ns, nd = np.empty(max(len(src), 1), np.uint32), np.empty(max(len(src), 1), np.uint32)
+            ref.ref_hashtable_map_edges(self.h, src, dst, len(src), ns, nd)
+            return ns[: len(src)], nd[: len(src)]

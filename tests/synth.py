@@ -1,0 +1,65 @@
+"""Seeded synthetic graphs of the BASELINE.json shapes (numpy, for tests and CPU-side checks).
+
+Degree sequence: discrete power law clipped to [0, max_deg] and rescaled so that sum(deg) ~= E;
+neighbour lists are sorted, ids uniform over V.  Features are a counter hash
+of (row, col) so any row can be re-derived without a second copy; labels = node % num_class.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+SEED = 0x5A4D47524150
+
+
+def power_law_degrees(rng, V, E, alpha=2.1, max_deg=None):
+    max_deg = max_deg or max(16, int(V ** 0.5) * 4)
+    u = rng.random(V)
+    d = np.floor((1.0 - u) ** (-1.0 / (alpha - 1.0))).astype(np.float64)
+    d = np.minimum(d, max_deg)
+    d *= E / d.sum()
+    deg = np.floor(d).astype(np.int64)
+    # a share of isolated / low-degree nodes keeps the deg <= fanout branch exercised
+    deg[rng.random(V) < 0.02] = 0
+    return np.minimum(deg, max_deg)
+
+
+def make_graph(V, E, seed=SEED, alpha=2.1, max_deg=None):
+    rng = np.random.default_rng(seed)
+    deg = power_law_degrees(rng, V, E, alpha, max_deg)
+    indptr = np.zeros(V + 1, np.uint32)
+    np.cumsum(deg, out=indptr[1:])
+    total = int(indptr[-1])
+    indices = rng.integers(0, V, size=total, dtype=np.uint32)
+    # sort inside each list
+    order = np.lexsort((indices, np.repeat(np.arange(V, dtype=np.uint32), deg)))
+    indices = indices[order]
+    return indptr, indices
+
+
+def feature_rows(rows: np.ndarray, dim: int, dtype=np.float32) -> np.ndarray:
+    """counter hash of (row, col) -> exact values representable in fp16/fp32."""
+    r = rows.astype(np.uint64)[:, None]
+    c = np.arange(dim, dtype=np.uint64)[None, :]
+    h = (r * np.uint64(0x9E3779B97F4A7C15) + c * np.uint64(0xD1B54A32D192ED03)) >> np.uint64(40)
+    v = (h % np.uint64(2048)).astype(np.float32) / np.float32(8.0) - np.float32(128.0)
+    return v.astype(dtype)
+
+
+def make_features(V, dim, dtype=np.float32):
+    return feature_rows(np.arange(V), dim, dtype)
+
+
+def make_labels(V, num_class=47):
+    return (np.arange(V, dtype=np.int64) % num_class).astype(np.int64)
+
+
+def train_set(V, frac, seed=SEED):
+    rng = np.random.default_rng(seed ^ 0xABCDEF)
+    perm = rng.permutation(V).astype(np.uint32)
+    return perm[: max(1, int(V * frac))]
+
+
+def degree_rank(indptr):
+    """nodes by out-degree, descending, stable (utility/data-process/toolkit/cache/cache_by_degree.cc:29-63)"""
+    deg = np.diff(indptr.astype(np.int64))
+    return np.argsort(-deg, kind="stable").astype(np.uint32)

@@ -1,0 +1,296 @@
+"""GPU parity tests of the single operators, through the C-ABI (xgnn_b200.ops -> ctypes -> libxgnn_b200.so),
+against the CPU oracle (oracle/oracle.c) and the committed reference fixtures (tests/golden/)."""
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+import oracle_lib as O
+import synth
+
+pytestmark = pytest.mark.gpu
+GOLD = np.load(Path(__file__).parent / "golden" / "ref_path_small.npz")
+
+
+def dev(a):
+    a = np.ascontiguousarray(a)
+    if a.dtype == np.uint32:
+        a = a.view(np.int32)
+    return torch.from_numpy(a).cuda()
+
+
+def host(t):
+    a = t.detach().cpu().numpy()
+    return a.view(np.uint32) if a.dtype == np.int32 else a
+
+
+@pytest.fixture(scope="module")
+def ops():
+    from xgnn_b200 import ops as _ops
+    return _ops
+
+
+# ---- hash table ------------------------------------------------------------------------------
+def test_hashtable_golden(ops):
+    t = ops.OrderedHashTable(4000)
+    u1 = t.FillWithDuplicates(dev(GOLD["fill1"]))
+    assert np.array_equal(host(u1), GOLD["uniq1"])
+    u2 = t.FillWithDuplicates(dev(GOLD["fill2"]))
+    assert np.array_equal(host(u2), GOLD["uniq2"])
+    ns, nd = ops.GPUMapEdges(dev(GOLD["fill2"]), dev(GOLD["fill2"][::-1].copy()), t)
+    assert np.array_equal(host(ns), GOLD["map_src"])
+    assert np.array_equal(host(nd), GOLD["map_dst"])
+
+
+@pytest.mark.parametrize("fill", ["FillWithDupRevised", "FillWithDuplicates", "FillWithDupMutable"])
+@pytest.mark.parametrize("reuse", [False, True])
+def test_hashtable_reference_gtest_vectors(ops, fill, reuse):
+    """samgraph/unittest/test_hashmap.cc:84-276: set equality, prefix, no duplicates, SearchO2N bijection."""
+    t = ops.OrderedHashTable(4096)
+    if reuse:
+        t.FillWithDupRevised(dev(np.arange(100, 900, dtype=np.uint32)))
+        t.Reset()
+    seen = []
+    prev = np.empty(0, np.uint32)
+    orc = O.Table(4096)
+    for v in ([1, 2, 3, 4, 5, 2, 5, 1, 10, 233], [1, 2, 3, 6, 9, 2, 8, 1, 3, 7, 1023],
+              [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 1, 2, 3, 4, 5], list(range(1, 513))):
+        a = np.array(v, np.uint32)
+        seen.append(a)
+        getattr(t, fill)(dev(a)) if fill != "FillWithDuplicates" else t.FillWithDuplicates(dev(a))
+        orc.populate(a)
+        u = host(t.RefUnique())
+        assert t.NumItems() == len(u)
+        assert set(u.tolist()) == set(np.concatenate(seen).tolist())
+        assert len(set(u.tolist())) == len(u)
+        assert np.array_equal(u[: len(prev)], prev)
+        assert np.array_equal(host(t.SearchO2N(dev(u))), np.arange(len(u), dtype=np.uint32))
+        assert np.array_equal(u, orc.unique())  # stronger than the reference: first-occurrence order
+        prev = u
+
+
+@pytest.mark.parametrize("n,space", [(1, 10), (255, 50), (1025, 100000), (1_000_000, 300_000), (1_000_000, 1 << 31)])
+def test_hashtable_random_vs_oracle(ops, n, space):
+    rng = np.random.default_rng(n + space)
+    t = ops.OrderedHashTable(3 * n + 16)
+    orc = O.Table(3 * n + 16)
+    for rep in range(3):  # 3 x 1M random ids as in test_hashmap.cc:223-273
+        a = rng.integers(0, space, size=n).astype(np.uint32)
+        u = t.FillWithDuplicates(dev(a))
+        orc.populate(a)
+        assert np.array_equal(host(u), orc.unique())
+    src = orc.unique()[rng.integers(0, orc.num_items(), size=min(n, 200000))]
+    dst = orc.unique()[rng.integers(0, orc.num_items(), size=min(n, 200000))]
+    ns, nd = ops.GPUMapEdges(dev(src), dev(dst), t)
+    os_, od = orc.map_edges(src, dst)
+    assert np.array_equal(host(ns), os_) and np.array_equal(host(nd), od)
+    # absent ids are reported, not spun on
+    absent = np.array([space + 5, space + 77], np.uint32) if space < (1 << 31) else np.array([0xFFFFFFF0], np.uint32)
+    if not np.isin(absent, orc.unique()).any():
+        assert np.all(host(t.SearchO2N(dev(absent))) == O.EMPTY)
+
+
+def test_hashtable_fill_with_unique_and_empty(ops):
+    t = ops.OrderedHashTable(1000)
+    a = np.random.default_rng(0).permutation(500).astype(np.uint32)
+    t.FillWithUnique(dev(a))
+    assert t.NumItems() == 500
+    assert np.array_equal(host(t.RefUnique()), a)
+    u = t.FillWithDuplicates(dev(np.empty(0, np.uint32)))
+    assert np.array_equal(host(u), a)
+    b = np.array([7, 900, 7, 901], np.uint32)
+    u = t.FillWithDuplicates(dev(b))
+    assert np.array_equal(host(u), np.concatenate([a, [900, 901]]).astype(np.uint32))
+
+
+def test_hashtable_capacity_error(ops):
+    from xgnn_b200._clib import XgError
+    t = ops.OrderedHashTable(64)
+    with pytest.raises(XgError):
+        t.FillWithDuplicates(dev(np.arange(1000, dtype=np.uint32)))
+
+
+def test_hashtable_many_fills_fold(ops):
+    t = ops.OrderedHashTable(10000)
+    orc = O.Table(10000)
+    rng = np.random.default_rng(3)
+    for _ in range(150):  # more fills than the device-side counter history holds
+        a = rng.integers(0, 5000, size=40).astype(np.uint32)
+        t.FillWithDupRevised(dev(a))
+        orc.populate(a)
+    assert np.array_equal(host(t.RefUnique()), orc.unique())
+
+
+# ---- uniform sampler ---------------------------------------------------------------------------
+def test_khop_full_neighbourhood_golden(ops):
+    g = ops.make_graph(dev(GOLD["indptr"]), dev(GOLD["indices"]))
+    for st in (ops.kKHop0, ops.kKHop2, ops.kKHop3):
+        src, dst = ops.GPUSampleKHop(g, dev(GOLD["inp"]), int(GOLD["fanout"]), sample_type=st)
+        assert np.array_equal(host(src), GOLD["khop0_src"])
+        assert np.array_equal(host(dst), GOLD["khop0_dst"])
+
+
+@pytest.mark.parametrize("fanout", [1, 3, 5, 10, 15, 25, 40, 100, 200])
+def test_khop_structure_vs_oracle(ops, fanout):
+    """deg <= fanout: bit-exact CSR order; deg > fanout: exactly `fanout` DISTINCT positions of the list."""
+    indptr, indices = synth.make_graph(20000, 400000, seed=5, max_deg=300)
+    # make neighbour ids unique per list position so that distinct positions are observable
+    rng = np.random.default_rng(1)
+    inp = rng.integers(0, 20000, size=7001).astype(np.uint32)
+    g = ops.make_graph(dev(indptr), dev(indices))
+    src, dst = ops.GPUSampleKHop(g, dev(inp), fanout, seed=9, batch_key=4)
+    src, dst = host(src), host(dst)
+    counts = np.minimum(np.diff(indptr.astype(np.int64))[inp], fanout)
+    assert len(src) == counts.sum()
+    assert np.array_equal(src, np.repeat(inp, counts))
+    osrc, odst = O.sample_khop0(indptr, indices, inp, fanout)
+    assert np.array_equal(src, osrc)
+    off = np.concatenate([[0], np.cumsum(counts)])
+    deg = np.diff(indptr.astype(np.int64))
+    for i in range(0, len(inp), 13):
+        v = inp[i]
+        lst = indices[indptr[v]: indptr[v + 1]]
+        got = dst[off[i]: off[i + 1]]
+        if deg[v] <= fanout:
+            assert np.array_equal(got, lst)
+            assert np.array_equal(got, odst[off[i]: off[i + 1]])
+        else:
+            # multiset inclusion: got must be a sub-multiset of lst
+            lu, lc = np.unique(lst, return_counts=True)
+            gu, gc = np.unique(got, return_counts=True)
+            assert np.isin(gu, lu).all()
+            assert (gc <= lc[np.searchsorted(lu, gu)]).all()
+    # reproducible for the same (seed, batch_key), different otherwise
+    s2, d2 = ops.GPUSampleKHop(g, dev(inp), fanout, seed=9, batch_key=4)
+    assert np.array_equal(host(d2), dst)
+    if (deg[inp] > fanout).sum() > 50:
+        s3, d3 = ops.GPUSampleKHop(g, dev(inp), fanout, seed=9, batch_key=5)
+        assert not np.array_equal(host(d3), dst)
+
+
+@pytest.mark.parametrize("deg,fanout", [(7, 3), (20, 5), (40, 15), (33, 32), (200, 25), (70, 40)])
+def test_khop_selection_frequency_chi_square(ops, deg, fanout):
+    """Per-edge inclusion frequency is uniform f/deg (north_star: chi-square when fanout < degree)."""
+    reps = 20000
+    indptr = np.array([0, deg], np.uint32)
+    indices = np.arange(100, 100 + deg, dtype=np.uint32)
+    g = ops.make_graph(dev(indptr), dev(indices))
+    inp = np.zeros(reps, np.uint32)  # the same node `reps` times: every position has its own RNG counter
+    src, dst = ops.GPUSampleKHop(g, dev(inp), fanout, seed=123, batch_key=1)
+    dst = host(dst).reshape(reps, fanout) - 100
+    # no repeats inside a sample
+    assert (np.sort(dst, axis=1)[:, 1:] != np.sort(dst, axis=1)[:, :-1]).all()
+    obs = np.bincount(dst.ravel(), minlength=deg).astype(np.float64)
+    p = fanout / deg
+    # each position is included with prob p independently across reps: z-score per edge, chi2 over edges
+    var = reps * p * (1 - p)
+    chi2 = ((obs - reps * p) ** 2 / var).sum()
+    # inclusion indicators are negatively correlated with sum fixed -> chi2 ~ (deg-1) dof scaled by deg/(deg-1)
+    from scipy import stats
+    crit = stats.chi2.ppf(1 - 1e-6, deg - 1) * deg / (deg - 1)
+    assert chi2 < crit, (chi2, crit)
+    # pairwise: joint inclusion of (0,1) should be f(f-1)/(deg(deg-1))
+    both = ((dst == 0).any(axis=1) & (dst == 1).any(axis=1)).mean()
+    want = fanout * (fanout - 1) / (deg * (deg - 1))
+    assert abs(both - want) < 6 * np.sqrt(max(want * (1 - want), 1e-9) / reps) + 1e-9
+
+
+def test_khop_empty_and_isolated(ops):
+    indptr = np.array([0, 0, 3, 3], np.uint32)
+    indices = np.array([5, 6, 7], np.uint32)
+    g = ops.make_graph(dev(indptr), dev(indices))
+    src, dst = ops.GPUSampleKHop(g, dev(np.array([0, 2, 0], np.uint32)), 4)
+    assert len(src) == 0
+    src, dst = ops.GPUSampleKHop(g, dev(np.empty(0, np.uint32)), 4)
+    assert len(src) == 0
+    src, dst = ops.GPUSampleKHop(g, dev(np.array([0, 1, 2, 1], np.uint32)), 4)
+    assert host(src).tolist() == [1, 1, 1, 1, 1, 1] and host(dst).tolist() == [5, 6, 7, 5, 6, 7]
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 8])
+@pytest.mark.parametrize("ratio", [0.0, 0.4, 1.0])
+def test_khop_ggms_routed_equals_flat(ops, P, ratio):
+    """DeviceDistGraph routing (cuda/dist_graph.h:141-151): partitioned store returns the flat graph's lists."""
+    indptr, indices = synth.make_graph(6000, 60000, seed=8, max_deg=80)
+    ncn = O.num_cache_node(indptr, ratio)
+    parts = [O.partition_csr(indptr, indices, ncn, p, P) for p in range(P)]
+    d_parts = [(dev(pi), dev(px) if len(px) else torch.zeros(1, dtype=torch.int32, device="cuda")) for pi, px in parts]
+    # host slot: pinned whole graph, read through UVA
+    h_indptr = torch.from_numpy(indptr.view(np.int32)).pin_memory()
+    h_indices = torch.from_numpy(indices.view(np.int32)).pin_memory()
+    g = ops.make_graph(part_indptr=[a for a, _ in d_parts], part_indices=[b for _, b in d_parts], num_cache_node=ncn,
+                       num_node=6000, host_indptr=h_indptr, host_indices=h_indices)
+    flat = ops.make_graph(dev(indptr), dev(indices))
+    inp = np.random.default_rng(2).integers(0, 6000, size=3000).astype(np.uint32)
+    for fanout in (5, 100):
+        a = ops.GPUSampleKHop(g, dev(inp), fanout, seed=1, batch_key=2)
+        b = ops.GPUSampleKHop(flat, dev(inp), fanout, seed=1, batch_key=2)
+        assert np.array_equal(host(a[0]), host(b[0])) and np.array_equal(host(a[1]), host(b[1]))
+    torch.cuda.synchronize()
+
+
+# ---- extraction ------------------------------------------------------------------------------
+def test_extract_golden(ops):
+    V = len(GOLD["indptr"]) - 1
+    idx = dev(GOLD["idx"])
+    assert np.array_equal(host(ops.GPUExtract(dev(synth.make_features(V, 100, np.float32)), idx)), GOLD["x32"])
+    x16 = ops.GPUExtract(dev(synth.make_features(V, 24, np.float16)), idx)
+    assert np.array_equal(host(x16).view(np.uint16), GOLD["x16"].view(np.uint16))
+    assert np.array_equal(host(ops.GPUExtract(dev(synth.make_labels(V)), idx)), GOLD["xl"])
+
+
+@pytest.mark.parametrize("dtype,dim", [(np.float32, 100), (np.float32, 128), (np.float32, 256), (np.float16, 768),
+                                       (np.float16, 3), (np.uint8, 7), (np.int64, 1), (np.float64, 5), (np.int32, 1),
+                                       (np.float32, 1), (np.float32, 602)])
+def test_extract_bit_exact_all_dtypes(ops, dtype, dim):
+    rng = np.random.default_rng(dim)
+    V = 50000
+    tab = rng.integers(0, 255, size=(V, dim)).astype(dtype)
+    idx = rng.integers(0, V, size=33333).astype(np.uint32)
+    out = ops.GPUExtract(dev(tab), dev(idx))
+    want = O.extract(tab, idx)
+    assert np.array_equal(host(out).view(np.uint8), want.view(np.uint8))
+    assert ops.GPUExtract(dev(tab), dev(np.empty(0, np.uint32))).shape[0] == 0
+
+
+def test_extract_from_pinned_host_labels(ops):
+    """DoGPULabelExtract: dim=1 i64 gather straight from host memory (dist/dist_loops.cc:938-974)."""
+    lab = synth.make_labels(100000)
+    h = torch.from_numpy(lab).pin_memory()
+    idx = np.random.default_rng(0).integers(0, 100000, size=8000).astype(np.uint32)
+    out = ops.GPUExtract(h.data_ptr(), dev(idx), dim=1, dtype=torch.int64)
+    assert np.array_equal(host(out), lab[idx])
+
+
+@pytest.mark.parametrize("P", [1, 2, 8])
+@pytest.mark.parametrize("pct", [0.0, 0.3, 1.0])
+def test_extract_ggms_vs_oracle(ops, P, pct):
+    V, dim = 40000, 128
+    feat = synth.make_features(V, dim)
+    indptr, _ = synth.make_graph(V, 300000, seed=4)
+    rank = synth.degree_rank(indptr)
+    ncached = int(V * pct)
+    table = O.build_cache_table(rank, ncached, V)
+    parts = [O.partition_features(feat, rank, ncached, p, P) for p in range(P)]
+    d_parts = [dev(p) if len(p) else torch.zeros((1, dim), device="cuda") for p in parts]
+    h_feat = torch.from_numpy(feat).pin_memory()
+    store = ops.make_feature_store(dim * 4, h_feat, dev(table), d_parts, local_parts=(0,))
+    nodes = np.random.default_rng(7).integers(0, V, size=50001).astype(np.uint32)
+    stats = torch.zeros(4, dtype=torch.int64, device="cuda")
+    out = ops.ExtractGGMS(store, dev(nodes), dim, torch.float32, stats=stats)
+    want = O.extract_ggms(feat, nodes, table, parts)
+    assert np.array_equal(host(out).view(np.uint32), want.view(np.uint32))
+    ms, md, cs, cd = O.miss_cache_index(table, nodes)
+    st = stats.cpu().numpy()
+    assert st[2] == len(ms) and st[0] + st[1] == len(cs)
+    assert st[0] == (cs % P == 0).sum()
+    # the reference's three-step form gives the same rows
+    gms, gmd, gcs, gcd = ops.GetMissCacheIndex(dev(table), dev(nodes))
+    assert np.array_equal(host(gms), ms) and np.array_equal(host(gmd), md)
+    assert np.array_equal(host(gcs), cs) and np.array_equal(host(gcd), cd)
+    out2 = torch.empty_like(out)
+    ops.GPUExtractMissData(out2, h_feat, gms, gmd, dim * 4)
+    ops.CombineCacheData(out2, store, gcs, gcd)
+    assert torch.equal(out, out2)
+    torch.cuda.synchronize()

@@ -1,0 +1,168 @@
+"""CPU: pins the oracle (oracle/oracle.c) against
+  (1) the committed golden fixtures generated from the reference's own CPU code (tests/golden/make_golden.py),
+  (2) the reference's own code when oracle/_ref/libxgnn_ref.so is present (this container, or shipped prebuilt),
+  (3) the reference's gtest vectors for OrderedHashTable (samgraph/unittest/test_hashmap.cc:84-276).
+"""
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+import synth
+
+GOLD = np.load(Path(__file__).parent / "golden" / "ref_path_small.npz")
+needs_ref = pytest.mark.skipif(O.ref is None, reason="oracle/_ref not built (no /root/reference here)")
+
+
+# ---- (1) golden fixtures ----------------------------------------------------------------------
+def test_khop0_full_neighbourhood_matches_golden():
+    src, dst = O.sample_khop0(GOLD["indptr"], GOLD["indices"], GOLD["inp"], int(GOLD["fanout"]))
+    assert np.array_equal(src, GOLD["khop0_src"])
+    assert np.array_equal(dst, GOLD["khop0_dst"])
+
+
+def test_hashtable0_matches_golden():
+    t = O.Table(4000)
+    t.populate(GOLD["fill1"])
+    assert np.array_equal(t.unique(), GOLD["uniq1"])
+    t.populate(GOLD["fill2"])
+    assert np.array_equal(t.unique(), GOLD["uniq2"])
+    ms, md = t.map_edges(GOLD["fill2"], GOLD["fill2"][::-1].copy())
+    assert np.array_equal(ms, GOLD["map_src"])
+    assert np.array_equal(md, GOLD["map_dst"])
+
+
+def test_extract_matches_golden():
+    V = len(GOLD["indptr"]) - 1
+    idx = GOLD["idx"]
+    assert np.array_equal(O.extract(synth.make_features(V, 100, np.float32), idx), GOLD["x32"])
+    assert np.array_equal(O.extract(synth.make_features(V, 24, np.float16), idx).view(np.uint16),
+                          GOLD["x16"].view(np.uint16))
+    assert np.array_equal(O.extract(synth.make_labels(V), idx), GOLD["xl"])
+
+
+def test_minibatch_matches_golden():
+    f = int(GOLD["b_fanout"])
+    mb = O.minibatch(GOLD["b_indptr"], GOLD["b_indices"], GOLD["b_seeds"], [f, f, f], seed=3)
+    counts = GOLD["b_counts"].reshape(3, 3)
+    for l in range(3):
+        assert (mb["num_src"][l], mb["num_dst"][l], mb["num_edge"][l]) == tuple(int(x) for x in counts[l])
+        assert np.array_equal(mb["row"][l], GOLD[f"b_row{l}"])
+        assert np.array_equal(mb["col"][l], GOLD[f"b_col{l}"])
+    assert np.array_equal(mb["input_nodes"], GOLD["b_input_nodes"])
+    feat = O.extract(synth.make_features(4000, 16, np.float32), mb["input_nodes"])
+    assert np.array_equal(feat, GOLD["b_feat"])
+    assert np.array_equal(O.extract(synth.make_labels(4000), GOLD["b_seeds"]), GOLD["b_label"])
+    assert sum(mb["num_edge"]) == int(GOLD["b_total"])
+
+
+# ---- (2) live reference ------------------------------------------------------------------------
+@needs_ref
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_oracle_vs_reference_live(seed):
+    rng = np.random.default_rng(seed)
+    indptr, indices = synth.make_graph(5000, 40000, seed=seed, max_deg=40)
+    inp = rng.integers(0, 5000, size=900).astype(np.uint32)
+    fan = int(np.diff(indptr.astype(np.int64)).max())
+    rs, rd = O.ref_sample_khop0(indptr, indices, inp, fan)
+    os_, od = O.sample_khop0(indptr, indices, inp, fan)
+    assert np.array_equal(rs, os_) and np.array_equal(rd, od)
+    # small fanout: sizes and src agree; dst must be real neighbours
+    rs, rd = O.ref_sample_khop0(indptr, indices, inp, 5)
+    os_, od = O.sample_khop0(indptr, indices, inp, 5)
+    assert np.array_equal(rs, os_)
+    rt, ot = O.RefTable(0, 6000), O.Table(6000)
+    for _ in range(3):
+        a = rng.integers(0, 5000, size=2000).astype(np.uint32)
+        rt.populate(a)
+        ot.populate(a)
+        assert np.array_equal(rt.unique(), ot.unique())
+    a = rt.unique()[rng.integers(0, rt.num_items(), size=3000)]
+    b = rt.unique()[rng.integers(0, rt.num_items(), size=3000)]
+    r1, r2 = rt.map_edges(a, b)
+    o1, o2 = ot.map_edges(a, b)
+    assert np.array_equal(r1, o1) and np.array_equal(r2, o2)
+    for dt, dim in ((np.float32, 100), (np.float16, 768), (np.int64, 1), (np.uint8, 7)):
+        tab = (rng.integers(0, 100, size=(5000, dim)) if dim > 1 else rng.integers(0, 100, size=5000)).astype(dt)
+        idx = rng.integers(0, 5000, size=333).astype(np.uint32)
+        assert np.array_equal(O.ref_extract(tab, idx), O.extract(tab, idx))
+
+
+@needs_ref
+def test_reference_hashtable2_is_set_equal():
+    """CPUHashTable2 (arch0 default) has a racy winner: only the SET and the prefix property hold."""
+    rng = np.random.default_rng(5)
+    rt, ot = O.RefTable(2, 6000), O.Table(6000)
+    a = rng.integers(0, 5000, size=4000).astype(np.uint32)
+    rt.populate(a)
+    ot.populate(a)
+    assert np.array_equal(np.sort(rt.unique()), np.sort(ot.unique()))
+
+
+# ---- (3) reference gtest vectors (unittest/test_hashmap.cc:98-117,168-195) ----------------------
+def _check_unique_props(t, inputs_so_far, prev_unique):
+    u = t.unique()
+    assert set(u.tolist()) == set(np.concatenate(inputs_so_far).tolist())
+    assert len(set(u.tolist())) == len(u)
+    assert np.array_equal(u[: len(prev_unique)], prev_unique)
+    assert np.array_equal(t.lookup(u), np.arange(len(u), dtype=np.uint32))
+    return u.copy()
+
+
+def test_reference_gtest_vectors_on_oracle():
+    t = O.Table(2048)
+    v1 = np.array([1, 2, 3, 4, 5, 2, 5, 1, 10, 233], np.uint32)
+    v2 = np.array([1, 2, 3, 6, 9, 2, 8, 1, 3, 7, 1023], np.uint32)
+    t.populate(v1)
+    u1 =_check_unique_props(t, [v1], np.empty(0, np.uint32))
+    t.populate(v2)
+    _check_unique_props(t, [v1, v2], u1)
+    t.reset()
+    v3 = np.array([1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 1, 2, 3, 4, 5], np.uint32)
+    t.populate(v3)
+    u3 = _check_unique_props(t, [v3], np.empty(0, np.uint32))
+    assert len(u3) == 13
+    v4 = np.arange(1, 513, dtype=np.uint32)
+    t.populate(v4)
+    _check_unique_props(t, [v3, v4], u3)
+
+
+# ---- routing / partition restatements: self-consistency ------------------------------------------
+@pytest.mark.parametrize("P", [1, 2, 3, 8])
+def test_partitioned_topology_reassembles(P):
+    indptr, indices = synth.make_graph(2000, 16000, seed=11, max_deg=50)
+    for ratio in (0.0, 0.37, 1.0):
+        ncn = O.num_cache_node(indptr, ratio)
+        want = int(int(indptr[-1]) * ratio)
+        assert ncn == 0 or indptr[ncn - 1] < want
+        assert indptr[ncn] >= want or ncn == 2000
+        parts = [O.partition_csr(indptr, indices, ncn, p, P) for p in range(P)]
+        for v in range(0, 2000, 7):
+            p, r = O.route_node(v, P, ncn)
+            lst = indices[indptr[v]: indptr[v + 1]]
+            if v < ncn:
+                assert (p, r) == (v % P, v // P)
+                pi, px = parts[p]
+                assert np.array_equal(px[pi[r]: pi[r + 1]], lst)
+            else:
+                assert (p, r) == (P, v)
+
+
+@pytest.mark.parametrize("P", [1, 4])
+def test_partitioned_features_reassemble(P):
+    V, dim = 3000, 12
+    feat = synth.make_features(V, dim)
+    indptr, _ = synth.make_graph(V, 20000, seed=4)
+    rank = synth.degree_rank(indptr)
+    ncached = 1700
+    table = O.build_cache_table(rank, ncached, V)
+    parts = [O.partition_features(feat, rank, ncached, p, P) for p in range(P)]
+    nodes = np.random.default_rng(0).integers(0, V, size=5000).astype(np.uint32)
+    out = O.extract_ggms(feat, nodes, table, parts)
+    assert np.array_equal(out, feat[nodes])
+    ms, md, cs, cd = O.miss_cache_index(table, nodes)
+    assert len(ms) + len(cs) == len(nodes)
+    assert np.array_equal(nodes[md], ms) and np.all(table[ms] == O.EMPTY)
+    assert np.array_equal(table[nodes[cd]], cs)
+    assert np.all(np.diff(md.astype(np.int64)) > 0) and np.all(np.diff(cd.astype(np.int64)) > 0)

@@ -1,0 +1,114 @@
+"""ctypes loader for libxgnn_b200.so (the C-ABI declared in include/xgnn_b200.h and
+include/samgraph_abi.h).  Mirrors how the reference loads its own C library:
+samgraph/common/__init__.py:280-362 (ctypes.CDLL(path, RTLD_GLOBAL) + explicit arg/restypes).
+
+There is NO fallback: if the CUDA library is missing this module raises at import time.
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import (POINTER, Structure, c_char_p, c_double, c_int, c_size_t, c_uint32, c_uint64,
+                    c_void_p)
+from pathlib import Path
+
+XG_MAX_PARTS = 16
+XG_EMPTY_KEY = 0xFFFFFFFF
+
+LIB_PATH = Path(__file__).resolve().parent / "lib" / "libxgnn_b200.so"
+
+
+class XgGraph(Structure):
+    _fields_ = [
+        ("part_indptr", c_void_p * (XG_MAX_PARTS + 1)),
+        ("part_indices", c_void_p * (XG_MAX_PARTS + 1)),
+        ("num_part", c_uint32),
+        ("num_cache_node", c_uint32),
+        ("num_node", c_uint32),
+        ("reserved", c_uint32),
+    ]
+
+
+class XgFeatureStore(Structure):
+    _fields_ = [
+        ("part", c_void_p * XG_MAX_PARTS),
+        ("host", c_void_p),
+        ("cache_table", c_void_p),
+        ("num_part", c_uint32),
+        ("local_part_mask", c_uint32),
+        ("row_bytes", c_uint64),
+    ]
+
+
+def _load() -> ctypes.CDLL:
+    if not LIB_PATH.exists():
+        raise ImportError(
+            f"{LIB_PATH} is missing: build it with `python -m xgnn_b200.build` "
+            "(xgnn_b200 has no CPU fallback)")
+    return ctypes.CDLL(str(LIB_PATH), mode=ctypes.RTLD_GLOBAL)
+
+
+lib = _load()
+
+_u32p = c_void_p  # device pointers are passed as integers
+
+
+def _sig(name, restype, *argtypes):
+    fn = getattr(lib, name)
+    fn.restype = restype
+    fn.argtypes = list(argtypes)
+    return fn
+
+
+# ---- core -----------------------------------------------------------------------------------
+_sig("xg_last_error", c_char_p)
+_sig("xg_version", c_int)
+_sig("xg_launch_count", c_uint64)
+
+# ---- hash table -----------------------------------------------------------------------------
+_sig("xg_hashtable_create", c_int, POINTER(c_void_p), c_size_t, c_int)
+_sig("xg_hashtable_destroy", c_int, c_void_p)
+_sig("xg_hashtable_reset", c_int, c_void_p, c_void_p)
+_sig("xg_hashtable_fill_with_unique", c_int, c_void_p, _u32p, c_size_t, c_void_p)
+_sig("xg_hashtable_fill_with_dup_revised", c_int, c_void_p, _u32p, c_size_t, c_void_p)
+_sig("xg_hashtable_fill_with_dup_mutable", c_int, c_void_p, _u32p, c_size_t, c_void_p)
+_sig("xg_hashtable_fill_with_duplicates", c_int, c_void_p, _u32p, c_size_t, _u32p, POINTER(c_uint32), c_void_p)
+_sig("xg_hashtable_ref_unique", c_int, c_void_p, POINTER(c_void_p), POINTER(c_uint32))
+_sig("xg_hashtable_copy_unique", c_int, c_void_p, _u32p, c_void_p)
+_sig("xg_hashtable_num_items", c_size_t, c_void_p)
+_sig("xg_hashtable_lookup", c_int, c_void_p, _u32p, c_size_t, _u32p, c_void_p)
+_sig("xg_map_edges", c_int, c_void_p, _u32p, _u32p, _u32p, _u32p, c_size_t, c_void_p)
+
+# ---- samplers -------------------------------------------------------------------------------
+_sig("xg_sample_khop", c_int, POINTER(XgGraph), c_int, _u32p, c_size_t, c_size_t, _u32p, _u32p, c_void_p,
+     c_uint64, c_uint64, c_void_p)
+
+# ---- extraction -----------------------------------------------------------------------------
+_sig("xg_extract", c_int, c_void_p, c_void_p, _u32p, c_size_t, c_size_t, c_int, c_void_p)
+_sig("xg_extract_ggms", c_int, POINTER(XgFeatureStore), _u32p, c_size_t, c_void_p, c_void_p, c_void_p)
+_sig("xg_get_miss_cache_index", c_int, _u32p, _u32p, c_size_t, _u32p, _u32p, POINTER(c_size_t), _u32p, _u32p,
+     POINTER(c_size_t), c_void_p)
+_sig("xg_extract_miss_data", c_int, c_void_p, c_void_p, _u32p, _u32p, c_size_t, c_size_t, c_void_p)
+_sig("xg_combine_cache_data", c_int, c_void_p, POINTER(XgFeatureStore), _u32p, _u32p, c_size_t, c_void_p)
+
+
+class XgError(RuntimeError):
+    pass
+
+
+def check(rc: int) -> None:
+    if rc != 0:
+        raise XgError(f"xgnn_b200 error {rc}: {lib.xg_last_error().decode()}")
+
+
+def declared_symbols() -> list[str]:
+    """Every extern "C" symbol the headers under include/ declare (parsed from the headers)."""
+    import re
+    names: list[str] = []
+    inc = Path(__file__).resolve().parent.parent / "include"
+    for h in sorted(inc.glob("*.h")):
+        text = re.sub(r"/\*.*?\*/", "", h.read_text(), flags=re.S)
+        text = re.sub(r"//[^\n]*", "", text)
+        for m in re.finditer(r"\b((?:xg|samgraph)_[A-Za-z0-9_]+)\s*\(", text):
+            if m.group(1) not in names:
+                names.append(m.group(1))
+    return names

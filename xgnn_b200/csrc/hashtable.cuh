@@ -1,0 +1,94 @@
+// Device-side view of the ordered hash table (unique + remap).
+//
+// Replaces DeviceOrderedHashTable / MutableDeviceOrderedHashTable
+// (reference: samgraph/common/cuda/cuda_hashtable.h:35-101, cuda_hashtable.cu:36-135).
+//
+// Layout in HBM (all per table, sized once for the worst-case batch):
+//   slots : uint2 {key, val}[capacity]   capacity = pow2 >= 2 * max_items, 0xFFFFFFFF'FFFFFFFF = free
+//   n2o   : uint32[max_items]            local id -> global id  (the "unique" list, append only)
+//   items : uint32[kMaxFills + 1]        items[k] = number of unique ids after the k-th fill since
+//                                        Reset (items[0] = 0); lives on the device so that a whole
+//                                        minibatch can be enqueued without a host round trip.
+//
+// Determinism: while a fill is in flight `val` of a NEW key holds 0x80000000 | (smallest input
+// position that carries the key) -- maintained with atomicMin -- so the occurrence that numbers
+// the key is the FIRST in input order, not whichever CAS lands first as in the reference
+// (cuda_hashtable.cu:54-79).  Keys from earlier fills hold their local id (< 2^31), which atomicMin
+// against a tagged position can never change.
+#pragma once
+#include "common.cuh"
+
+namespace xg {
+
+constexpr int kMaxFills = 62;
+constexpr uint32_t kPosTag = 0x80000000u;
+
+struct TableView {
+  uint2 *slots;
+  uint32_t *n2o;
+  uint32_t *items;     // [kMaxFills + 1]
+  uint32_t *overflow;  // set to 1 if capacity was exceeded
+  uint32_t mask;       // capacity - 1
+  uint32_t n2o_cap;
+};
+
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t table_hash(uint32_t k) {
+  // murmur3 finaliser: full avalanche so that consecutive node ids do not form probe clusters
+  k ^= k >> 16; k *= 0x85EBCA6Bu; k ^= k >> 13; k *= 0xC2B2AE35u; k ^= k >> 16;
+  return k;
+}
+
+// Claim (or find) the slot of `key`; fold `tagged_pos` into its val with atomicMin.
+// Returns the slot position, or kEmpty if the table is full.
+__device__ __forceinline__ uint32_t table_insert(const TableView &t, uint32_t key, uint32_t tagged_pos) {
+  uint32_t p = table_hash(key) & t.mask;
+  for (uint32_t probes = 0; probes <= t.mask; ++probes) {
+    uint32_t *kp = &t.slots[p].x;
+    uint32_t k = *reinterpret_cast<volatile uint32_t *>(kp);
+    if (k == kEmpty) k = atomicCAS(kp, kEmpty, key);
+    if (k == kEmpty || k == key) {
+      atomicMin(&t.slots[p].y, tagged_pos);
+      return p;
+    }
+    p = (p + 1) & t.mask;
+  }
+  *t.overflow = 1;
+  return kEmpty;
+}
+
+// SearchO2N: slot position of `key`, kEmpty when absent.
+__device__ __forceinline__ uint32_t table_find(const TableView &t, uint32_t key) {
+  uint32_t p = table_hash(key) & t.mask;
+  for (uint32_t probes = 0; probes <= t.mask; ++probes) {
+    uint32_t k = __ldg(&t.slots[p].x);
+    if (k == key) return p;
+    if (k == kEmpty) return kEmpty;
+    p = (p + 1) & t.mask;
+  }
+  return kEmpty;
+}
+#endif
+
+// host-side launchers shared by hashtable.cu and the minibatch pipeline
+struct ScanSpace {      // zeroed before every launch that uses it
+  uint32_t *ticket;     // 1 word (padded to 8 B)
+  uint64_t *state;      // one word per tile
+  size_t max_tiles;
+};
+
+constexpr int kAssignBlock = 256;
+constexpr int kAssignItems = 4;
+constexpr int kAssignTile = kAssignBlock * kAssignItems;
+
+// insert keys[0..n) with positions 0..n-1; pos_out[i] = slot position. n from *d_n if d_n != NULL.
+int launch_table_insert(const TableView &t, const uint32_t *keys, uint32_t *pos_out, size_t n_max,
+                        const uint64_t *d_n, cudaStream_t s);
+// number the first occurrences: items[fill] = items[fill-1] + #new; n2o appended; slot.val = local
+int launch_table_assign(const TableView &t, const uint32_t *pos, size_t n_max, const uint64_t *d_n,
+                        int fill, const ScanSpace &scan, cudaStream_t s);
+// out[i] = slots[pos[i]].val
+int launch_table_gather_local(const TableView &t, const uint32_t *pos, uint32_t *out, size_t n_max,
+                              const uint64_t *d_n, cudaStream_t s);
+
+}  // namespace xg

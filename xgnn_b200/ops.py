@@ -1,0 +1,221 @@
+"""Operator-level Python mirror of the reference's CUDA operators, over the `xg_*` C-ABI.
+
+torch is used for device memory and streams only.  ids are int32 tensors viewing uint32 (as the
+reference exposes them, samgraph/torch/adapter.cc:86-120).  Names follow the reference:
+OrderedHashTable (cuda/cuda_hashtable.h:103), GPUSampleKHop0/3 (cuda/cuda_function.h),
+GPUMapEdges (cuda/cuda_mapping.cu:68), GPUExtract (cuda/cuda_extraction.cu:74),
+GetMissCacheIndex / CombineCacheData / GPUExtractMissData (cuda/cuda_cache_manager.h).
+"""
+from __future__ import annotations
+
+import ctypes
+from ctypes import byref, c_size_t, c_uint32, c_void_p
+
+import torch
+
+from . import _clib
+from ._clib import XG_EMPTY_KEY, XG_MAX_PARTS, XgFeatureStore, XgGraph, check, lib
+
+kKHop0, kKHop1, kWeightedKHop, kRandomWalk, kWeightedKHopPrefix, kKHop2, kWeightedKHopHashDedup, kKHop3 = range(8)
+_DTYPE_CODE = {torch.float32: 0, torch.float64: 1, torch.float16: 2, torch.uint8: 3, torch.int32: 4,
+               torch.int8: 5, torch.int64: 6, torch.bfloat16: 2}
+
+
+def _ptr(t: torch.Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ids(t: torch.Tensor) -> torch.Tensor:
+    assert t.dtype == torch.int32 and t.is_contiguous(), "ids must be contiguous int32 (uint32 view)"
+    return t
+
+
+class OrderedHashTable:
+    """cuda::OrderedHashTable (cuda/cuda_hashtable.h:103-153) with first-occurrence numbering."""
+
+    def __init__(self, size: int, device: int | torch.device = 0):
+        self.device = torch.device("cuda", device) if isinstance(device, int) else device
+        h = c_void_p()
+        check(lib.xg_hashtable_create(byref(h), size, self.device.index or 0))
+        self._h = h
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.xg_hashtable_destroy(self._h)
+            self._h = None
+
+    def Reset(self):
+        check(lib.xg_hashtable_reset(self._h, _stream()))
+
+    def FillWithUnique(self, input: torch.Tensor):
+        check(lib.xg_hashtable_fill_with_unique(self._h, _ptr(_ids(input)), input.numel(), _stream()))
+
+    def FillWithDupRevised(self, input: torch.Tensor):
+        check(lib.xg_hashtable_fill_with_dup_revised(self._h, _ptr(_ids(input)), input.numel(), _stream()))
+
+    def FillWithDupMutable(self, input: torch.Tensor):
+        check(lib.xg_hashtable_fill_with_dup_mutable(self._h, _ptr(_ids(input)), input.numel(), _stream()))
+
+    def FillWithDuplicates(self, input: torch.Tensor, unique: torch.Tensor | None = None) -> torch.Tensor:
+        """Returns the unique list (old prefix + new ids)."""
+        n_old = self.NumItems()
+        if unique is None:
+            unique = torch.empty(n_old + input.numel(), dtype=torch.int32, device=self.device)
+        n = c_uint32(0)
+        check(lib.xg_hashtable_fill_with_duplicates(self._h, _ptr(_ids(input)), input.numel(), _ptr(unique),
+                                                    byref(n), _stream()))
+        return unique[: n.value]
+
+    def NumItems(self) -> int:
+        return int(lib.xg_hashtable_num_items(self._h))
+
+    def RefUnique(self) -> torch.Tensor:
+        """Copy of the table-resident unique list (the reference hands out the raw pointer)."""
+        p = c_void_p()
+        n = c_uint32(0)
+        check(lib.xg_hashtable_ref_unique(self._h, byref(p), byref(n)))
+        out = torch.empty(n.value, dtype=torch.int32, device=self.device)
+        check(lib.xg_hashtable_copy_unique(self._h, _ptr(out), _stream()))
+        return out
+
+    def CopyUnique(self, unique: torch.Tensor):
+        check(lib.xg_hashtable_copy_unique(self._h, _ptr(unique), _stream()))
+
+    def SearchO2N(self, ids: torch.Tensor) -> torch.Tensor:
+        out = torch.empty_like(ids)
+        check(lib.xg_hashtable_lookup(self._h, _ptr(_ids(ids)), ids.numel(), _ptr(out), _stream()))
+        return out
+
+    @property
+    def handle(self):
+        return self._h
+
+
+def GPUMapEdges(global_src: torch.Tensor, global_dst: torch.Tensor, table: OrderedHashTable):
+    """cuda::GPUMapEdges (cuda/cuda_mapping.cu:68-80) -> (new_src, new_dst)."""
+    new_src = torch.empty_like(global_src)
+    new_dst = torch.empty_like(global_dst)
+    check(lib.xg_map_edges(table.handle, _ptr(_ids(global_src)), _ptr(new_src), _ptr(_ids(global_dst)),
+                           _ptr(new_dst), global_src.numel(), _stream()))
+    return new_src, new_dst
+
+
+def make_graph(indptr: torch.Tensor | None = None, indices: torch.Tensor | None = None, *,
+               part_indptr=None, part_indices=None, num_cache_node: int = 0, num_node: int | None = None,
+               host_indptr: torch.Tensor | int | None = None,
+               host_indices: torch.Tensor | int | None = None) -> XgGraph:
+    """Flat (DeviceNormalGraph) or sharded (DeviceDistGraph) topology handle, cuda/dist_graph.h:114-180.
+    Partition entries may be tensors or raw device pointers (ints, e.g. IPC-mapped peer memory)."""
+    g = XgGraph()
+
+    def p(x):
+        return x if isinstance(x, int) or x is None else x.data_ptr()
+
+    if part_indptr is None:
+        g.part_indptr[0] = p(indptr)
+        g.part_indices[0] = p(indices)
+        g.num_part = 0
+        g.num_cache_node = 0
+        g.num_node = (indptr.numel() - 1) if num_node is None else num_node
+    else:
+        P = len(part_indptr)
+        assert P <= XG_MAX_PARTS
+        for i in range(P):
+            g.part_indptr[i] = p(part_indptr[i])
+            g.part_indices[i] = p(part_indices[i])
+        g.part_indptr[P] = p(host_indptr)
+        g.part_indices[P] = p(host_indices)
+        g.num_part = P
+        g.num_cache_node = num_cache_node
+        g.num_node = num_node or 0
+    return g
+
+
+def GPUSampleKHop(graph: XgGraph, input: torch.Tensor, fanout: int, *, seed: int = 0, batch_key: int = 0,
+                  sample_type: int = kKHop0):
+    """GPUSampleKHop0/2/3<GraphType> (cuda/cuda_sampling_khop0.cu:243-335, khop3.cu:234-318).
+    Returns (out_src, out_dst) already trimmed to num_out (this wrapper reads the count back)."""
+    n = input.numel()
+    out_src = torch.empty(max(n * fanout, 1), dtype=torch.int32, device=input.device)
+    out_dst = torch.empty(max(n * fanout, 1), dtype=torch.int32, device=input.device)
+    num_out = torch.zeros(1, dtype=torch.int64, device=input.device)
+    check(lib.xg_sample_khop(byref(graph), sample_type, _ptr(_ids(input)), n, fanout, _ptr(out_src), _ptr(out_dst),
+                             _ptr(num_out), seed, batch_key, _stream()))
+    e = int(num_out.item())
+    return out_src[:e], out_dst[:e]
+
+
+def GPUExtract(src: torch.Tensor | int, index: torch.Tensor, dim: int | None = None,
+               dtype: torch.dtype | None = None) -> torch.Tensor:
+    """cuda::GPUExtract (cuda/cuda_extraction.cu:74-116). `src` is a [num_node, dim] tensor on the device or in
+    pinned host memory (read through UVA), or a raw pointer with dim/dtype given."""
+    if isinstance(src, torch.Tensor):
+        dtype = src.dtype
+        dim = src.shape[1] if src.dim() == 2 else 1
+        sp = src.data_ptr()
+    else:
+        sp = src
+    shape = (index.numel(), dim) if dim != 1 or (isinstance(src, torch.Tensor) and src.dim() == 2) else (index.numel(),)
+    out = torch.empty(shape, dtype=dtype, device=index.device)
+    check(lib.xg_extract(_ptr(out), sp, _ptr(_ids(index)), index.numel(), dim, _DTYPE_CODE[dtype], _stream()))
+    return out
+
+
+def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_table: torch.Tensor | None = None,
+                       parts=None, local_parts=()) -> XgFeatureStore:
+    """DeviceDistFeature + cache table + host table in one handle (cuda/dist_graph.h:182-213)."""
+    st = XgFeatureStore()
+
+    def p(x):
+        return x if isinstance(x, int) or x is None else x.data_ptr()
+
+    st.host = p(host)
+    st.cache_table = p(cache_table)
+    st.row_bytes = row_bytes
+    parts = parts or []
+    assert len(parts) <= XG_MAX_PARTS
+    for i, t in enumerate(parts):
+        st.part[i] = p(t)
+    st.num_part = len(parts)
+    mask = 0
+    for i in local_parts:
+        mask |= 1 << i
+    st.local_part_mask = mask
+    return st
+
+
+def ExtractGGMS(store: XgFeatureStore, nodes: torch.Tensor, dim: int, dtype: torch.dtype,
+                stats: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
+    """GetMissCacheIndex + GPUExtractMissData + CombineCacheData fused (one launch)."""
+    if out is None:
+        out = torch.empty((nodes.numel(), dim), dtype=dtype, device=nodes.device)
+    check(lib.xg_extract_ggms(byref(store), _ptr(_ids(nodes)), nodes.numel(), _ptr(out), _ptr(stats), _stream()))
+    return out
+
+
+def GetMissCacheIndex(cache_table: torch.Tensor, nodes: torch.Tensor):
+    """GPUCacheManager::GetMissCacheIndex (cuda/cuda_cache_manager_device.cu:355-441)
+    -> (miss_src, miss_dst, cache_src, cache_dst)."""
+    n = nodes.numel()
+    bufs = [torch.empty(max(n, 1), dtype=torch.int32, device=nodes.device) for _ in range(4)]
+    nm, nc = c_size_t(0), c_size_t(0)
+    check(lib.xg_get_miss_cache_index(_ptr(cache_table), _ptr(_ids(nodes)), n, _ptr(bufs[0]), _ptr(bufs[1]), byref(nm),
+                                      _ptr(bufs[2]), _ptr(bufs[3]), byref(nc), _stream()))
+    return bufs[0][: nm.value], bufs[1][: nm.value], bufs[2][: nc.value], bufs[3][: nc.value]
+
+
+def GPUExtractMissData(out: torch.Tensor, host_feat: torch.Tensor | int, miss_src, miss_dst, row_bytes: int):
+    sp = host_feat if isinstance(host_feat, int) else host_feat.data_ptr()
+    check(lib.xg_extract_miss_data(_ptr(out), sp, _ptr(miss_src), _ptr(miss_dst), miss_src.numel(), row_bytes, _stream()))
+
+
+def CombineCacheData(out: torch.Tensor, store: XgFeatureStore, cache_src, cache_dst):
+    check(lib.xg_combine_cache_data(_ptr(out), byref(store), _ptr(cache_src), _ptr(cache_dst), cache_src.numel(), _stream()))
+
+
+def launch_count() -> int:
+    return int(lib.xg_launch_count())
