@@ -132,6 +132,8 @@ def make_graph(indptr: torch.Tensor | None = None, indices: torch.Tensor | None 
         g.num_part = P
         g.num_cache_node = num_cache_node
         g.num_node = num_node or 0
+    # the handle holds raw pointers: keep the tensors behind them alive as long as the handle lives
+    g._keep = [indptr, indices, part_indptr, part_indices, host_indptr, host_indices]
     return g
 
 
@@ -185,6 +187,7 @@ def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_ta
     for i in local_parts:
         mask |= 1 << i
     st.local_part_mask = mask
+    st._keep = [host, cache_table, parts]  # raw pointers inside: keep the tensors alive
     return st
 
 
