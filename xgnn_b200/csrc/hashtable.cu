@@ -40,8 +40,12 @@ table_fill_unique_kernel(TableView t, const uint32_t *__restrict__ keys, size_t 
     const uint32_t key = keys[i];
     const uint32_t local = base + (uint32_t)i;
     uint32_t p = table_insert(t, key, local);  // local < 2^31 < any tag: atomicMin keeps it
-    if (p != kEmpty && local < t.n2o_cap) t.n2o[local] = key;
-    else *t.overflow = 1;
+    if (p != kEmpty && local < t.n2o_cap) {
+      t.n2o[local] = key;
+      t.n2o_slot[local] = p;
+    } else {
+      *t.overflow = 1;
+    }
   }
   if (blockIdx.x == 0 && threadIdx.x == 0) t.items[fill] = base + (uint32_t)n;
 }
@@ -121,6 +125,7 @@ table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, size_t n_max,
         if (local < t.n2o_cap) {
           t.slots[slot_pos[k]].y = local;
           t.n2o[local] = slot[k].x;
+          t.n2o_slot[local] = slot_pos[k];
         } else {
           *t.overflow = 1;
         }
@@ -128,6 +133,16 @@ table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, size_t n_max,
     }
     __syncthreads();  // s_tile / s_cnt are reused by the next tile
   }
+}
+
+// Targeted Reset: free exactly the slots the finished batch numbered (the reference bumps a
+// version word instead, cuda_hashtable.cu:739-742; 8-byte slots have no room for one).
+__global__ void __launch_bounds__(256)
+table_clear_kernel(TableView t, int fill) {
+  const uint32_t n = min(t.items[fill], t.n2o_cap);
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n;
+       i += (uint64_t)gridDim.x * blockDim.x)
+    t.slots[t.n2o_slot[i]] = make_uint2(kEmpty, kEmpty);
 }
 
 __global__ void __launch_bounds__(256)
@@ -174,6 +189,15 @@ int launch_table_assign(const TableView &t, const uint32_t *pos, size_t n_max, c
   return XG_OK;
 }
 
+int launch_table_clear(const TableView &t, int fill, size_t max_items, cudaStream_t s) {
+  if (fill > 0) {
+    table_clear_kernel<<<grid_for((max_items + 255) / 256, 8), 256, 0, s>>>(t, fill);
+    XG_LAUNCHED();
+  }
+  XG_CUDA(cudaMemsetAsync(t.items, 0, (kMaxFills + 2) * sizeof(uint32_t), s));
+  return XG_OK;
+}
+
 int launch_table_gather_local(const TableView &t, const uint32_t *pos, uint32_t *out, size_t n_max,
                               const uint64_t *d_n, cudaStream_t s) {
   if (n_max == 0) return XG_OK;
@@ -200,6 +224,7 @@ struct xg_hashtable {
   void *scan_mem = nullptr;  // ticket + state words
   size_t scan_tiles = 0;
   cudaStream_t last_stream = nullptr;
+  bool dirty_full = false;  // an overflow was seen: the next Reset wipes the whole table
 };
 
 namespace {
@@ -277,6 +302,7 @@ int check_overflow(xg_hashtable *t, cudaStream_t s) {
   XG_CUDA(cudaMemcpyAsync(&ovf, t->view.overflow, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
   XG_CUDA(cudaStreamSynchronize(s));
   if (ovf) {
+    t->dirty_full = true;
     set_error("hash table capacity exceeded (max_items=" + std::to_string(t->max_items) + ")");
     return XG_ERR_CAPACITY;
   }
@@ -309,6 +335,7 @@ int xg_hashtable_create(xg_hashtable **out, size_t max_items, int device) {
   t->capacity = next_pow2(max_items * 2);
   XG_CUDA(cudaMalloc(&t->view.slots, t->capacity * sizeof(uint2)));
   XG_CUDA(cudaMalloc(&t->view.n2o, max_items * sizeof(uint32_t)));
+  XG_CUDA(cudaMalloc(&t->view.n2o_slot, max_items * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&t->view.items, (kMaxFills + 2) * sizeof(uint32_t)));
   t->view.overflow = t->view.items + kMaxFills + 1;
   t->view.mask = static_cast<uint32_t>(t->capacity - 1);
@@ -324,6 +351,7 @@ int xg_hashtable_destroy(xg_hashtable *t) {
   DeviceGuard guard(t->device);
   cudaFree(t->view.slots);
   cudaFree(t->view.n2o);
+  cudaFree(t->view.n2o_slot);
   cudaFree(t->view.items);
   cudaFree(t->scratch);
   cudaFree(t->scan_mem);
@@ -335,8 +363,14 @@ int xg_hashtable_reset(xg_hashtable *t, void *stream) {
   XG_REQUIRE(t != nullptr, "table is NULL");
   DeviceGuard guard(t->device);
   cudaStream_t s = as_stream(stream);
-  XG_CUDA(cudaMemsetAsync(t->view.slots, 0xFF, t->capacity * sizeof(uint2), s));
-  XG_CUDA(cudaMemsetAsync(t->view.items, 0, (kMaxFills + 2) * sizeof(uint32_t), s));
+  if (t->dirty_full) {
+    XG_CUDA(cudaMemsetAsync(t->view.slots, 0xFF, t->capacity * sizeof(uint2), s));
+    XG_CUDA(cudaMemsetAsync(t->view.items, 0, (kMaxFills + 2) * sizeof(uint32_t), s));
+    t->dirty_full = false;
+  } else {
+    int rc = launch_table_clear(t->view, t->fill, t->max_items, s);
+    if (rc) return rc;
+  }
   t->fill = 0;
   t->last_stream = s;
   return XG_OK;

@@ -26,6 +26,7 @@ constexpr uint32_t kPosTag = 0x80000000u;
 struct TableView {
   uint2 *slots;
   uint32_t *n2o;
+  uint32_t *n2o_slot;  // [max_items] slot position of every numbered key: lets Reset clear only those
   uint32_t *items;     // [kMaxFills + 1]
   uint32_t *overflow;  // set to 1 if capacity was exceeded
   uint32_t mask;       // capacity - 1
@@ -87,6 +88,8 @@ int launch_table_insert(const TableView &t, const uint32_t *keys, uint32_t *pos_
 // number the first occurrences: items[fill] = items[fill-1] + #new; n2o appended; slot.val = local
 int launch_table_assign(const TableView &t, const uint32_t *pos, size_t n_max, const uint64_t *d_n,
                         int fill, const ScanSpace &scan, cudaStream_t s);
+// Reset in O(items): slots[n2o_slot[i]] = free for i < items[fill], then items[] = 0 (stream-ordered)
+int launch_table_clear(const TableView &t, int fill, size_t max_items, cudaStream_t s);
 // out[i] = slots[pos[i]].val
 int launch_table_gather_local(const TableView &t, const uint32_t *pos, uint32_t *out, size_t n_max,
                               const uint64_t *d_n, cudaStream_t s);
