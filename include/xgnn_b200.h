@@ -171,6 +171,130 @@ int xg_extract_miss_data(void *d_out, const void *host_feat, const uint32_t *d_m
 int xg_combine_cache_data(void *d_out, const xg_feature_store *store, const uint32_t *d_cache_src,
                           const uint32_t *d_cache_dst, size_t num_cache, void *stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Minibatch engine: one call enqueues what dist::DoGPUSample (dist/dist_loops.cc:62-368),
+ * DoGPULabelExtract (:938-974), DoArch6GetCacheMissIndex (:1015-1074) and
+ * DoArch6GPUCacheFeatureCopy (:1209-1285) do for one Task -- hash table Reset, seed fill, per layer
+ * sample + unique + remap, then the routed feature gather and the label gather -- as ONE replayed
+ * CUDA graph with every count kept on the device; the only host round trip is the final 128-byte
+ * read of the counts.
+ */
+#define XG_MAX_LAYERS 8
+#define XG_SAMPLER_NO_GRAPH 1u /* flags: launch the kernels one by one instead of replaying a graph */
+#define XG_SAMPLER_STAGE_TIMING 2u /* flags: (implies NO_GRAPH) CUDA events around every stage */
+
+/* stages of one minibatch, for xg_batch_stage_ms */
+enum {
+  XG_STAGE_RESET_SEEDS = 0, /* Reset + FillWithDupRevised(seeds) */
+  XG_STAGE_SAMPLE = 1,      /* per layer: sample kernel (with the fused hash insert) */
+  XG_STAGE_NUMBER = 2,      /* per layer: number first occurrences (unique list append) */
+  XG_STAGE_REMAP = 3,       /* per layer: neighbour local ids */
+  XG_STAGE_INPUT_NODES = 4, /* input_nodes copy + counts */
+  XG_STAGE_FEATURE = 5,     /* routed feature gather */
+  XG_STAGE_LABEL = 6,       /* label gather */
+};
+
+typedef struct xg_sampler_config {
+  uint32_t num_layer;
+  uint32_t fanout[XG_MAX_LAYERS]; /* indexed by layer; consumed last -> first (dist_loops.cc:120-123) */
+  uint32_t batch_size;            /* most seeds one minibatch can carry */
+  int32_t sample_type;            /* XG_KHOP0 / XG_KHOP2 / XG_KHOP3 */
+  uint32_t num_slots;             /* minibatches that may be alive at once; 0 -> 2 */
+  uint32_t flags;
+  uint32_t feat_dim;
+  int32_t feat_dtype;             /* XG_F32 ...; row_bytes of the store must equal dim * sizeof(dtype) */
+  uint64_t seed;
+  uint64_t max_input_nodes;       /* 0 -> PredictNumNodes(batch_size, fanout) (common.cc:488-497),
+                                     clipped to the number of nodes */
+  void *stream;                   /* cudaStream_t all work is enqueued on; NULL -> a private stream */
+} xg_sampler_config;
+
+/* One finished Task (common.h:246-285). Pointers are device pointers owned by the batch; they stay
+ * valid until xg_batch_release. Layer l = TrainGraph graphs[l]: graphs[num_layer-1] is the seed-side
+ * block, graphs[0] the input-side block (num_src[0] == num_input). */
+typedef struct xg_batch_view {
+  uint64_t key;
+  uint32_t num_layer;
+  uint32_t num_output; /* seeds */
+  uint32_t num_input;  /* input_nodes */
+  uint32_t reserved;
+  const uint32_t *row[XG_MAX_LAYERS];  /* local id of the sampled neighbour, < num_src */
+  const uint32_t *col[XG_MAX_LAYERS];  /* local id of the expanded node,     < num_dst */
+  const uint32_t *data[XG_MAX_LAYERS]; /* per-edge payload (random-walk visit counts) or NULL */
+  uint64_t num_src[XG_MAX_LAYERS];
+  uint64_t num_dst[XG_MAX_LAYERS];
+  uint64_t num_edge[XG_MAX_LAYERS];
+  const uint32_t *input_nodes;
+  const uint32_t *output_nodes;
+  const void *input_feat;      /* [num_input, feat_dim] or NULL when no feature store was given */
+  const int64_t *output_label; /* [num_output] or NULL */
+} xg_batch_view;
+
+typedef struct xg_sampler xg_sampler;
+typedef struct xg_batch xg_batch;
+
+/* `store` and `label` may be NULL (sampling only). `label` = int64[num_node], device or pinned host. */
+int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_store *store,
+                      const void *label, const xg_sampler_config *cfg, int device);
+int xg_sampler_destroy(xg_sampler *s);
+/* Enqueue one minibatch for `num_seeds` seeds (host pointer, or device pointer when
+ * seeds_on_device != 0). Returns at once; *out is claimed until xg_batch_release. */
+int xg_sampler_submit(xg_sampler *s, const uint32_t *seeds, size_t num_seeds, int seeds_on_device,
+                      uint64_t batch_key, xg_batch **out);
+/* Block until the batch is complete, then describe it. XG_ERR_CAPACITY if it outgrew its buffers. */
+int xg_batch_wait(xg_batch *b, xg_batch_view *view);
+int xg_batch_release(xg_batch *b);
+/* stream the sampler enqueues on (for events) and kernels per minibatch (for launch accounting) */
+void *xg_sampler_stream(xg_sampler *s);
+uint32_t xg_sampler_launches_per_batch(xg_sampler *s);
+/* device time of one stage of a finished batch (sampler created with XG_SAMPLER_STAGE_TIMING);
+ * `layer` is ignored for the stages that are not per layer */
+int xg_batch_stage_ms(xg_batch *b, int stage, int layer, float *ms);
+/* PredictNumNodes, common.cc:488-497 */
+size_t xg_predict_num_nodes(size_t batch_size, const uint32_t *fanout, size_t num_layer);
+
+/* ------------------------------------------------------------------------------------------------
+ * GGMS store plumbing (host side).
+ */
+/* std::shuffle(nodes, nodes + n, std::mt19937(n)): the cache-rank order of GPUCacheManager,
+ * cuda/cuda_cache_manager_host.cc:162-171 (same libstdc++ algorithm, hence the same order). */
+int xg_shuffle_cache_ranks(uint32_t *h_nodes, size_t num_cached);
+/* smallest n with indptr[n] >= floor(E * ratio): DistEngine::SampleDataCopy, dist/dist_engine.cc:223-232 */
+uint32_t xg_num_cache_node(const uint32_t *h_indptr, uint32_t num_node, double ratio);
+/* DistGraph::_DatasetPartition, cuda/dist_graph.cu:228-272, as two device passes around the caller's
+ * exclusive scan: rows = ceil((num_cache_node - part) / P); row j is node part + j * P. */
+size_t xg_part_num_rows(uint32_t num_cache_node, uint32_t part, uint32_t num_part);
+int xg_part_degrees(const uint32_t *d_indptr, uint32_t num_cache_node, uint32_t part, uint32_t num_part,
+                    uint32_t *d_deg_out, void *stream);
+int xg_part_copy_indices(const uint32_t *d_indptr, const uint32_t *d_indices, uint32_t num_cache_node, uint32_t part,
+                         uint32_t num_part, const uint32_t *d_part_indptr, uint32_t *d_part_indices, void *stream);
+/* DistGraph::_DataIpcShare, cuda/dist_graph.cu:274-307: shards come from their own cudaMalloc so that
+ * a 64-byte CUDA IPC handle names exactly one shard; peers map it and load from it inside kernels. */
+int xg_device_malloc(void **out, size_t bytes);
+int xg_device_free(void *p);
+int xg_ipc_export(const void *d_ptr, unsigned char out_handle[64]);
+int xg_ipc_import(const unsigned char handle[64], void **out);
+int xg_ipc_close(void *p);
+int xg_enable_peer_access(int device, int peer);
+
+/* ------------------------------------------------------------------------------------------------
+ * Synthetic datasets of the BASELINE.json shapes, generated in HBM (stand-in for datagen/ and
+ * utility/data-process/, which need the network). Pure functions of (node, slot, seed); a shard is
+ * the arithmetic sequence v = begin + i * stride (the GGMS partition v % P == p). numpy twins:
+ * tests/synth.py.
+ *   degree(v)       = min(max_deg, floor(c * sqrt(num_node / (v + 1))))
+ *   neighbour(v, j) = floor(num_node * u^2), u = hash(v, j, seed) / 2^32
+ *   feature(v, col) = ((v * K1 + col * K2) >> 40) % 2048 / 8 - 128      (exact in fp16 / fp32)
+ */
+int xg_synth_degrees(uint32_t *d_deg, uint64_t begin, uint64_t stride, size_t n, uint64_t num_node, double c,
+                     uint32_t max_deg, void *stream);
+/* d_indptr: the shard's own (rebased) CSR offsets, n + 1 entries */
+int xg_synth_indices(uint32_t *d_indices, const uint32_t *d_indptr, uint64_t begin, uint64_t stride, size_t n,
+                     uint64_t num_node, uint64_t seed, void *stream);
+/* rows = d_row_ids[i] when given, else begin + i * stride; dtype XG_F32 or XG_F16 */
+int xg_synth_features(void *d_out, const uint32_t *d_row_ids, uint64_t begin, uint64_t stride, size_t n_rows,
+                      uint32_t dim, int dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

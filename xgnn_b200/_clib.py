@@ -39,6 +39,45 @@ class XgFeatureStore(Structure):
     ]
 
 
+XG_MAX_LAYERS = 8
+
+
+class XgSamplerConfig(Structure):
+    _fields_ = [
+        ("num_layer", c_uint32),
+        ("fanout", c_uint32 * XG_MAX_LAYERS),
+        ("batch_size", c_uint32),
+        ("sample_type", c_int),
+        ("num_slots", c_uint32),
+        ("flags", c_uint32),
+        ("feat_dim", c_uint32),
+        ("feat_dtype", c_int),
+        ("seed", c_uint64),
+        ("max_input_nodes", c_uint64),
+        ("stream", c_void_p),
+    ]
+
+
+class XgBatchView(Structure):
+    _fields_ = [
+        ("key", c_uint64),
+        ("num_layer", c_uint32),
+        ("num_output", c_uint32),
+        ("num_input", c_uint32),
+        ("reserved", c_uint32),
+        ("row", c_void_p * XG_MAX_LAYERS),
+        ("col", c_void_p * XG_MAX_LAYERS),
+        ("data", c_void_p * XG_MAX_LAYERS),
+        ("num_src", c_uint64 * XG_MAX_LAYERS),
+        ("num_dst", c_uint64 * XG_MAX_LAYERS),
+        ("num_edge", c_uint64 * XG_MAX_LAYERS),
+        ("input_nodes", c_void_p),
+        ("output_nodes", c_void_p),
+        ("input_feat", c_void_p),
+        ("output_label", c_void_p),
+    ]
+
+
 def _load() -> ctypes.CDLL:
     if not LIB_PATH.exists():
         raise ImportError(
@@ -89,6 +128,33 @@ _sig("xg_get_miss_cache_index", c_int, _u32p, _u32p, c_size_t, _u32p, _u32p, POI
      POINTER(c_size_t), c_void_p)
 _sig("xg_extract_miss_data", c_int, c_void_p, c_void_p, _u32p, _u32p, c_size_t, c_size_t, c_void_p)
 _sig("xg_combine_cache_data", c_int, c_void_p, POINTER(XgFeatureStore), _u32p, _u32p, c_size_t, c_void_p)
+
+
+# ---- minibatch engine -----------------------------------------------------------------------
+_sig("xg_sampler_create", c_int, POINTER(c_void_p), POINTER(XgGraph), POINTER(XgFeatureStore), c_void_p,
+     POINTER(XgSamplerConfig), c_int)
+_sig("xg_sampler_destroy", c_int, c_void_p)
+_sig("xg_sampler_submit", c_int, c_void_p, c_void_p, c_size_t, c_int, c_uint64, POINTER(c_void_p))
+_sig("xg_batch_wait", c_int, c_void_p, POINTER(XgBatchView))
+_sig("xg_batch_release", c_int, c_void_p)
+_sig("xg_sampler_stream", c_void_p, c_void_p)
+_sig("xg_sampler_launches_per_batch", c_uint32, c_void_p)
+_sig("xg_batch_stage_ms", c_int, c_void_p, c_int, c_int, POINTER(ctypes.c_float))
+_sig("xg_synth_degrees", c_int, c_void_p, c_uint64, c_uint64, c_size_t, c_uint64, c_double, c_uint32, c_void_p)
+_sig("xg_synth_indices", c_int, c_void_p, c_void_p, c_uint64, c_uint64, c_size_t, c_uint64, c_uint64, c_void_p)
+_sig("xg_synth_features", c_int, c_void_p, c_void_p, c_uint64, c_uint64, c_size_t, c_uint32, c_int, c_void_p)
+_sig("xg_shuffle_cache_ranks", c_int, c_void_p, c_size_t)
+_sig("xg_num_cache_node", c_uint32, c_void_p, c_uint32, c_double)
+_sig("xg_part_num_rows", c_size_t, c_uint32, c_uint32, c_uint32)
+_sig("xg_part_degrees", c_int, c_void_p, c_uint32, c_uint32, c_uint32, c_void_p, c_void_p)
+_sig("xg_part_copy_indices", c_int, c_void_p, c_void_p, c_uint32, c_uint32, c_uint32, c_void_p, c_void_p, c_void_p)
+_sig("xg_device_malloc", c_int, POINTER(c_void_p), c_size_t)
+_sig("xg_device_free", c_int, c_void_p)
+_sig("xg_ipc_export", c_int, c_void_p, c_void_p)
+_sig("xg_ipc_import", c_int, c_void_p, POINTER(c_void_p))
+_sig("xg_ipc_close", c_int, c_void_p)
+_sig("xg_enable_peer_access", c_int, c_int, c_int)
+_sig("xg_predict_num_nodes", c_size_t, c_size_t, POINTER(c_uint32), c_size_t)
 
 
 class XgError(RuntimeError):

@@ -15,7 +15,7 @@
 //            8 independent 128-bit loads in flight per thread before the matching stores, so lanes
 //            are never idle on rows that are not a multiple of 512 B (e.g. 100 x fp32 = 25 chunks).
 // Local HBM, NVLink-peer HBM and pinned host rows take the same path; only the pointer differs.
-#include "common.cuh"
+#include "extract.cuh"
 
 namespace xg {
 
@@ -25,12 +25,6 @@ constexpr int kGatherBlock = 256;
 constexpr int kGatherUnroll = 8;
 constexpr int kGatherChunksPerTile = kGatherBlock * kGatherUnroll;  // 2048 chunks (32 KB at 16 B)
 constexpr int kGatherMaxRows = 256;                                  // rows per tile upper bound
-
-enum GatherMode : int {
-  kByNode = 0,   // idx = node id; cache_table decides cache vs host
-  kHostRow = 1,  // idx = row of store.host (miss list / plain GPUExtract)
-  kCacheRank = 2 // idx = cache rank (hit list)
-};
 
 template <int VW> struct Vec;
 template <> struct Vec<16> { using T = int4; };
@@ -74,13 +68,16 @@ __device__ __forceinline__ const char *route_row(const xg_feature_store &st, int
 template <int VW>
 __global__ void __launch_bounds__(kGatherBlock)
 gather_rows_kernel(const xg_feature_store st, int mode, const uint32_t *__restrict__ src_idx,
-                   const uint32_t *__restrict__ dst_idx, size_t num_rows, uint32_t rows_per_tile,
+                   const uint32_t *__restrict__ dst_idx, size_t num_rows_max,
+                   const uint32_t *__restrict__ d_num_rows, uint32_t rows_per_tile,
                    uint32_t chunks_per_row, char *__restrict__ out, unsigned long long *stats) {
   using V = typename Vec<VW>::T;
   __shared__ const char *s_src[kGatherMaxRows];
   __shared__ char *s_dst[kGatherMaxRows];
   __shared__ unsigned s_class[3];
 
+  size_t num_rows = num_rows_max;
+  if (d_num_rows && *d_num_rows < num_rows_max) num_rows = *d_num_rows;  // count still on the device
   const size_t num_tiles = (num_rows + rows_per_tile - 1) / rows_per_tile;
   for (size_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
     const size_t row0 = tile * rows_per_tile;
@@ -133,8 +130,10 @@ int pick_vector_width(const xg_feature_store &st, const void *out) {
   return 1;
 }
 
+}  // namespace
+
 int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx, const uint32_t *dst_idx,
-                  size_t num_rows, void *out, uint64_t *stats, cudaStream_t s) {
+                  size_t num_rows, const uint32_t *d_num_rows, void *out, uint64_t *stats, cudaStream_t s) {
   if (num_rows == 0) return XG_OK;
   XG_REQUIRE(st.row_bytes > 0, "row_bytes is 0");
   XG_REQUIRE(out != nullptr && src_idx != nullptr, "NULL buffer");
@@ -153,15 +152,17 @@ int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx,
   auto *o = static_cast<char *>(out);
   auto *st64 = reinterpret_cast<unsigned long long *>(stats);
   switch (vw) {
-    case 16: gather_rows_kernel<16><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, rows_per_tile, cpr, o, st64); break;
-    case 8: gather_rows_kernel<8><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, rows_per_tile, cpr, o, st64); break;
-    case 4: gather_rows_kernel<4><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, rows_per_tile, cpr, o, st64); break;
-    case 2: gather_rows_kernel<2><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, rows_per_tile, cpr, o, st64); break;
-    default: gather_rows_kernel<1><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, rows_per_tile, cpr, o, st64); break;
+    case 16: gather_rows_kernel<16><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
+    case 8: gather_rows_kernel<8><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
+    case 4: gather_rows_kernel<4><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
+    case 2: gather_rows_kernel<2><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
+    default: gather_rows_kernel<1><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
   }
   XG_LAUNCHED();
   return XG_OK;
 }
+
+namespace {
 
 // ---- GetMissCacheIndex: stable two-way split with one chained scan (both counts in one word) ----
 constexpr int kSplitBlock = 256;
@@ -251,11 +252,6 @@ SplitWorkspace g_split_ws[XG_MAX_PARTS * 4];
 
 }  // namespace
 
-int gather_by_node(const xg_feature_store &st, const uint32_t *d_nodes, size_t n, void *d_out,
-                   uint64_t *d_stats, cudaStream_t s) {
-  return launch_gather(st, kByNode, d_nodes, nullptr, n, d_out, d_stats, s);
-}
-
 }  // namespace xg
 
 using namespace xg;
@@ -276,13 +272,13 @@ int xg_extract(void *d_dst, const void *src, const uint32_t *d_index, size_t num
   xg_feature_store st{};
   st.host = src;
   st.row_bytes = dim * elem;
-  return launch_gather(st, kHostRow, d_index, nullptr, num_index, d_dst, nullptr, as_stream(stream));
+  return launch_gather(st, kHostRow, d_index, nullptr, num_index, nullptr, d_dst, nullptr, as_stream(stream));
 }
 
 int xg_extract_ggms(const xg_feature_store *store, const uint32_t *d_nodes, size_t num_nodes, void *d_out,
                     uint64_t *d_stats, void *stream) {
   XG_REQUIRE(store != nullptr, "store is NULL");
-  return launch_gather(*store, kByNode, d_nodes, nullptr, num_nodes, d_out, d_stats, as_stream(stream));
+  return launch_gather(*store, kByNode, d_nodes, nullptr, num_nodes, nullptr, d_out, d_stats, as_stream(stream));
 }
 
 int xg_extract_miss_data(void *d_out, const void *host_feat, const uint32_t *d_miss_src,
@@ -291,13 +287,13 @@ int xg_extract_miss_data(void *d_out, const void *host_feat, const uint32_t *d_m
   xg_feature_store st{};
   st.host = host_feat;
   st.row_bytes = row_bytes;
-  return launch_gather(st, kHostRow, d_miss_src, d_miss_dst, num_miss, d_out, nullptr, as_stream(stream));
+  return launch_gather(st, kHostRow, d_miss_src, d_miss_dst, num_miss, nullptr, d_out, nullptr, as_stream(stream));
 }
 
 int xg_combine_cache_data(void *d_out, const xg_feature_store *store, const uint32_t *d_cache_src,
                           const uint32_t *d_cache_dst, size_t num_cache, void *stream) {
   XG_REQUIRE(store != nullptr, "store is NULL");
-  return launch_gather(*store, kCacheRank, d_cache_src, d_cache_dst, num_cache, d_out, nullptr,
+  return launch_gather(*store, kCacheRank, d_cache_src, d_cache_dst, num_cache, nullptr, d_out, nullptr,
                        as_stream(stream));
 }
 

@@ -9,6 +9,7 @@
 // on 8-byte slots, all stream-ordered with device-resident counts (no host round trip).
 #include "hashtable.cuh"
 
+#include <cstdlib>
 #include <mutex>
 #include <vector>
 
@@ -332,7 +333,12 @@ int xg_hashtable_create(xg_hashtable **out, size_t max_items, int device) {
   auto *t = new xg_hashtable();
   t->device = device;
   t->max_items = max_items;
-  t->capacity = next_pow2(max_items * 2);
+  // slots per item: 2.0 by default (the reference's scale, cuda_hashtable.cu:146-149); XG_TABLE_LOAD_PCT
+  // trades probe length for footprint (a table that stays inside the 126 MB L2 probes much faster)
+  size_t pct = 200;
+  if (const char *e = std::getenv("XG_TABLE_SLOTS_PCT")) pct = std::strtoul(e, nullptr, 10);
+  if (pct < 110) pct = 110;
+  t->capacity = next_pow2(max_items * pct / 100);
   XG_CUDA(cudaMalloc(&t->view.slots, t->capacity * sizeof(uint2)));
   XG_CUDA(cudaMalloc(&t->view.n2o, max_items * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&t->view.n2o_slot, max_items * sizeof(uint32_t)));

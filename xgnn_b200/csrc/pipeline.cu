@@ -1,0 +1,551 @@
+// Minibatch engine (SURVEY.md rows a10 + the extract stage functions).
+//
+// Reference behaviour being replaced: dist::DoGPUSample (samgraph/common/dist/dist_loops.cc:62-368),
+// DoGPULabelExtract (:938-974), DoArch6GetCacheMissIndex (:1015-1074), DoArch6GPUCacheFeatureCopy
+// (:1209-1285).  There one Task costs ~35-40 host<->device control crossings per layer (launch +
+// StreamSync each), >= 8 workspace alloc/free per layer and a blocking D2H of every count.
+//
+// Here a Task is ONE stream-ordered chain with every count resident on the device:
+//   Reset (targeted clear) -> seed insert -> number -> per layer { sample+insert (fused) -> number ->
+//   local-id gather } -> input_nodes copy -> routed feature gather -> label gather -> 1 D2H of counts
+// All buffers are sized once for the worst-case batch (PredictNumNodes, common.cc:488-497) so the
+// chain has a fixed shape and is captured once per batch slot as a CUDA graph and replayed: one
+// launch call per minibatch, no host synchronisation until the consumer asks for the batch.
+#include <atomic>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#include "extract.cuh"
+#include "hashtable.cuh"
+#include "sampling.cuh"
+
+namespace xg {
+TableView table_view(xg_hashtable *t);
+}
+using namespace xg;
+
+namespace {
+
+struct BatchParams {  // written by the host, read by the kernels of one batch
+  uint64_t num_seeds;
+  uint32_t num_seeds32;
+  uint32_t pad;
+  uint2 rng_key;
+};
+
+struct BatchCounts {  // written by the kernels, read back once
+  uint64_t num_edge[XG_MAX_LAYERS];
+  uint32_t items[XG_MAX_LAYERS + 2];  // items[0] = 0, [1] = unique seeds, [2 + k] = after k-th expanded layer
+  uint32_t overflow;
+  uint32_t pad;
+};
+
+__global__ void collect_counts_kernel(TableView t, int num_fill, BatchCounts *out) {
+  const int i = threadIdx.x;
+  if (i <= num_fill) out->items[i] = t.items[i];
+  if (i == 0) out->overflow = *t.overflow;
+}
+
+__global__ void __launch_bounds__(256)
+copy_ids_kernel(uint32_t *__restrict__ dst, const uint32_t *__restrict__ src, size_t n_max,
+                const uint32_t *__restrict__ d_n) {
+  size_t n = *d_n < n_max ? *d_n : n_max;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    dst[i] = src[i];
+}
+
+size_t elem_bytes(int dtype) {
+  switch (dtype) {
+    case XG_F32: case XG_I32: return 4;
+    case XG_F64: case XG_I64: return 8;
+    case XG_F16: return 2;
+    case XG_U8: case XG_I8: return 1;
+    default: return 0;
+  }
+}
+
+}  // namespace
+
+struct xg_batch {
+  xg_sampler *owner = nullptr;
+  int index = 0;
+  std::atomic<int> claimed{0};
+  // device
+  uint32_t *seeds = nullptr, *seed_local = nullptr, *input_nodes = nullptr;
+  uint32_t *row[XG_MAX_LAYERS] = {}, *col[XG_MAX_LAYERS] = {};
+  void *feat = nullptr;
+  int64_t *label = nullptr;
+  BatchParams *d_params = nullptr;
+  BatchCounts *d_counts = nullptr;
+  // pinned host
+  BatchParams *h_params = nullptr;
+  BatchCounts *h_counts = nullptr;
+  uint32_t *h_seeds = nullptr;
+  cudaEvent_t done = nullptr;
+  cudaGraphExec_t graph = nullptr;
+  uint64_t key = 0;
+  uint32_t num_seeds = 0;
+  bool recorded = false;  // `done` has been recorded at least once
+  std::vector<cudaEvent_t> marks;  // stage boundaries (XG_SAMPLER_STAGE_TIMING only)
+  int num_marks = 0;
+};
+
+struct xg_sampler {
+  int device = 0;
+  xg_graph graph{};
+  xg_feature_store store{};
+  bool has_store = false;
+  const void *label = nullptr;
+  xg_sampler_config cfg{};
+  size_t cap_in[XG_MAX_LAYERS] = {};    // most input nodes of layer l
+  size_t cap_edge[XG_MAX_LAYERS] = {};  // most sampled edges of layer l
+  size_t cap_input = 0;                 // most input_nodes of a batch
+  size_t row_bytes = 0;
+  xg_hashtable *table = nullptr;
+  TableView view{};
+  uint32_t *dst_global = nullptr, *pos = nullptr;  // per-layer scratch, reused layer after layer
+  void *scan_mem = nullptr;
+  size_t scan_bytes = 0, scan_tiles_a = 0, scan_tiles_b = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  bool use_graph = true;
+  bool stage_timing = false;
+  uint32_t launches_per_batch = 0;
+  std::mutex mu;
+  std::vector<xg_batch *> slots;
+  std::atomic<bool> dirty{false};  // a batch overflowed: unnumbered keys may be left in the table
+};
+
+namespace {
+
+ScanSpace scan_a(xg_sampler *s) {
+  auto *w = reinterpret_cast<uint64_t *>(s->scan_mem);
+  return ScanSpace{reinterpret_cast<uint32_t *>(w), w + 1, s->scan_tiles_a};
+}
+ScanSpace scan_b(xg_sampler *s) {
+  auto *w = reinterpret_cast<uint64_t *>(s->scan_mem) + 1 + s->scan_tiles_a;
+  return ScanSpace{reinterpret_cast<uint32_t *>(w), w + 1, s->scan_tiles_b};
+}
+
+int alloc_slot(xg_sampler *s, xg_batch **out) {
+  auto *b = new xg_batch();
+  b->owner = s;
+  const uint32_t L = s->cfg.num_layer;
+  const size_t B = s->cfg.batch_size;
+  XG_CUDA(cudaMalloc(&b->seeds, B * sizeof(uint32_t)));
+  XG_CUDA(cudaMalloc(&b->seed_local, B * sizeof(uint32_t)));
+  XG_CUDA(cudaMalloc(&b->input_nodes, s->cap_input * sizeof(uint32_t)));
+  for (uint32_t l = 0; l < L; ++l) {
+    XG_CUDA(cudaMalloc(&b->row[l], s->cap_edge[l] * sizeof(uint32_t)));
+    XG_CUDA(cudaMalloc(&b->col[l], s->cap_edge[l] * sizeof(uint32_t)));
+  }
+  if (s->has_store) XG_CUDA(cudaMalloc(&b->feat, s->cap_input * s->row_bytes));
+  if (s->label) XG_CUDA(cudaMalloc(&b->label, B * sizeof(int64_t)));
+  XG_CUDA(cudaMalloc(&b->d_params, sizeof(BatchParams)));
+  XG_CUDA(cudaMalloc(&b->d_counts, sizeof(BatchCounts)));
+  XG_CUDA(cudaMemset(b->d_counts, 0, sizeof(BatchCounts)));
+  XG_CUDA(cudaHostAlloc(&b->h_params, sizeof(BatchParams), cudaHostAllocDefault));
+  XG_CUDA(cudaHostAlloc(&b->h_counts, sizeof(BatchCounts), cudaHostAllocDefault));
+  XG_CUDA(cudaHostAlloc(&b->h_seeds, B * sizeof(uint32_t), cudaHostAllocDefault));
+  XG_CUDA(cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming));
+  if (s->stage_timing) {
+    b->marks.resize(5 + 3 * L);
+    for (auto &e : b->marks) XG_CUDA(cudaEventCreate(&e));
+  }
+  *out = b;
+  return XG_OK;
+}
+
+void free_slot(xg_batch *b) {
+  if (!b) return;
+  if (b->graph) cudaGraphExecDestroy(b->graph);
+  if (b->done) cudaEventDestroy(b->done);
+  for (auto e : b->marks) cudaEventDestroy(e);
+  cudaFree(b->seeds);
+  cudaFree(b->seed_local);
+  cudaFree(b->input_nodes);
+  for (int l = 0; l < XG_MAX_LAYERS; ++l) {
+    cudaFree(b->row[l]);
+    cudaFree(b->col[l]);
+  }
+  cudaFree(b->feat);
+  cudaFree(b->label);
+  cudaFree(b->d_params);
+  cudaFree(b->d_counts);
+  cudaFreeHost(b->h_params);
+  cudaFreeHost(b->h_counts);
+  cudaFreeHost(b->h_seeds);
+  delete b;
+}
+
+// The whole Task, stream-ordered; no host synchronisation, no allocation (capturable).
+int enqueue_batch(xg_sampler *s, xg_batch *b) {
+  cudaStream_t st = s->stream;
+  const int L = (int)s->cfg.num_layer;
+  const size_t B = s->cfg.batch_size;
+  const TableView &t = s->view;
+  const uint64_t *d_nseed64 = &b->d_params->num_seeds;
+  const uint32_t *d_nseed32 = &b->d_params->num_seeds32;
+
+  b->num_marks = 0;
+  auto mark = [&]() {
+    if (s->stage_timing && b->num_marks < (int)b->marks.size()) cudaEventRecord(b->marks[b->num_marks++], st);
+  };
+  mark();
+  // hash_table->Reset (dist_loops.cc:101): free the slots the previous batch numbered
+  int rc = launch_table_clear(t, L + 1, s->cap_input, st);
+  if (rc) return rc;
+  // FillWithDupRevised(output_nodes) (dist_loops.cc:106-107)
+  XG_CUDA(cudaMemsetAsync(s->scan_mem, 0, s->scan_bytes, st));
+  if ((rc = launch_table_insert(t, b->seeds, s->pos, B, d_nseed64, st))) return rc;
+  if ((rc = launch_table_assign(t, s->pos, B, d_nseed64, 1, scan_b(s), st))) return rc;
+  if ((rc = launch_table_gather_local(t, s->pos, b->seed_local, B, d_nseed64, st))) return rc;
+  mark();
+
+  for (int l = L - 1; l >= 0; --l) {  // seeds outward (dist_loops.cc:120-123)
+    const int fill = (L - 1 - l) + 2;
+    const bool seed_layer = (l == L - 1);
+    XG_CUDA(cudaMemsetAsync(s->scan_mem, 0, s->scan_bytes, st));
+    SampleFusion fusion{};
+    fusion.table = t;
+    fusion.pos_out = s->pos;
+    fusion.src_local = seed_layer ? b->seed_local : nullptr;  // later inputs ARE the unique list: local id == position
+    fusion.enabled = true;
+    uint64_t *d_num_edge = &b->d_counts->num_edge[l];
+    rc = launch_sample_uniform(s->graph, seed_layer ? b->seeds : t.n2o, s->cap_in[l],
+                               seed_layer ? d_nseed32 : &t.items[fill - 1], s->cfg.fanout[l], b->col[l],
+                               s->dst_global, d_num_edge, 0, 0, &b->d_params->rng_key,
+                               kSampleSalt + (uint32_t)l, fusion, scan_a(s), st);
+    if (rc) return rc;
+    mark();
+    // FillWithDuplicates(out_dst) + GPUMapEdges (dist_loops.cc:279-297): number the new ids, then
+    // one 8-byte load per edge at the remembered slot gives the neighbour's local id
+    if ((rc = launch_table_assign(t, s->pos, s->cap_edge[l], d_num_edge, fill, scan_b(s), st))) return rc;
+    mark();
+    if ((rc = launch_table_gather_local(t, s->pos, b->row[l], s->cap_edge[l], d_num_edge, st))) return rc;
+    mark();
+  }
+
+  // task->input_nodes = the unique list (dist_loops.cc:357); counts leave the table before the next Reset
+  copy_ids_kernel<<<grid_for((s->cap_input + 255) / 256, 4), 256, 0, st>>>(b->input_nodes, t.n2o, s->cap_input,
+                                                                         &t.items[L + 1]);
+  XG_LAUNCHED();
+  collect_counts_kernel<<<1, 32, 0, st>>>(t, L + 1, b->d_counts);
+  XG_LAUNCHED();
+  mark();
+  if (s->has_store) {  // DoArch6GetCacheMissIndex + DoArch6GPUCacheFeatureCopy in one launch
+    rc = launch_gather(s->store, kByNode, b->input_nodes, nullptr, s->cap_input, &b->d_counts->items[L + 1],
+                       b->feat, nullptr, st);
+    if (rc) return rc;
+  }
+  mark();
+  if (s->label) {  // DoGPULabelExtract: dim = 1, int64, straight from wherever the labels live
+    xg_feature_store ls{};
+    ls.host = s->label;
+    ls.row_bytes = sizeof(int64_t);
+    if ((rc = launch_gather(ls, kHostRow, b->seeds, nullptr, B, d_nseed32, b->label, nullptr, st))) return rc;
+  }
+  mark();
+  XG_CUDA(cudaMemcpyAsync(b->h_counts, b->d_counts, sizeof(BatchCounts), cudaMemcpyDeviceToHost, st));
+  return XG_OK;
+}
+
+struct DeviceScope {
+  int prev = 0, target = 0;
+  explicit DeviceScope(int dev) : target(dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceScope() {
+    if (prev != target) cudaSetDevice(prev);
+  }
+};
+
+}  // namespace
+
+extern "C" {
+
+size_t xg_predict_num_nodes(size_t batch_size, const uint32_t *fanout, size_t num_layer) {
+  size_t count = batch_size;
+  for (size_t i = num_layer; i-- > 0;) count += count * fanout[i];
+  return count;
+}
+
+int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_store *store,
+                      const void *label, const xg_sampler_config *cfg, int device) {
+  XG_REQUIRE(out && graph && cfg, "NULL argument");
+  XG_REQUIRE(cfg->num_layer >= 1 && cfg->num_layer <= XG_MAX_LAYERS, "num_layer must be in [1, 8]");
+  XG_REQUIRE(cfg->batch_size >= 1, "batch_size is 0");
+  XG_REQUIRE(cfg->sample_type == XG_KHOP0 || cfg->sample_type == XG_KHOP2 || cfg->sample_type == XG_KHOP3,
+             "the fused minibatch engine runs the uniform samplers (KHop0 / KHop2 / KHop3)");
+  XG_REQUIRE(graph->num_part <= XG_MAX_PARTS, "too many partitions");
+  DeviceScope scope(device);
+  auto *s = new xg_sampler();
+  s->device = device;
+  s->graph = *graph;
+  s->cfg = *cfg;
+  s->label = label;
+  if (store) {
+    s->store = *store;
+    s->has_store = true;
+    s->row_bytes = store->row_bytes;
+    const size_t eb = elem_bytes(cfg->feat_dtype);
+    if (eb == 0 || eb * cfg->feat_dim != store->row_bytes) {
+      delete s;
+      XG_REQUIRE(false, "feat_dim * sizeof(feat_dtype) must equal the store's row_bytes");
+    }
+  }
+  const int L = (int)cfg->num_layer;
+  size_t limit = cfg->max_input_nodes ? cfg->max_input_nodes
+                                      : xg_predict_num_nodes(cfg->batch_size, cfg->fanout, cfg->num_layer);
+  if (graph->num_node && limit > (size_t)graph->num_node + cfg->batch_size)
+    limit = (size_t)graph->num_node + cfg->batch_size;
+  size_t cur = cfg->batch_size;
+  for (int l = L - 1; l >= 0; --l) {
+    if (cfg->fanout[l] < 1 || cfg->fanout[l] > 512) {
+      delete s;
+      XG_REQUIRE(false, "fanout must be in [1, 512]");
+    }
+    s->cap_in[l] = cur;
+    s->cap_edge[l] = cur * cfg->fanout[l];
+    if (s->cap_edge[l] >= (1ull << 31)) {
+      delete s;
+      XG_REQUIRE(false, "a layer may hold at most 2^31 - 1 sampled edges");
+    }
+    cur = cur + s->cap_edge[l];
+    if (cur > limit) cur = limit;
+  }
+  s->cap_input = cur;
+  size_t max_edge = cfg->batch_size, tiles_a = 1, tiles_b = (cfg->batch_size + kAssignTile - 1) / kAssignTile;
+  for (int l = 0; l < L; ++l) {
+    if (s->cap_edge[l] > max_edge) max_edge = s->cap_edge[l];
+    const size_t ta = (s->cap_in[l] + kSampleTile - 1) / kSampleTile;
+    const size_t tb = (s->cap_edge[l] + kAssignTile - 1) / kAssignTile;
+    if (ta > tiles_a) tiles_a = ta;
+    if (tb > tiles_b) tiles_b = tb;
+  }
+  s->scan_tiles_a = tiles_a + 1;
+  s->scan_tiles_b = tiles_b + 1;
+  s->scan_bytes = (2 + s->scan_tiles_a + s->scan_tiles_b) * sizeof(uint64_t);
+
+  int rc = xg_hashtable_create(&s->table, s->cap_input, device);
+  if (rc) {
+    delete s;
+    return rc;
+  }
+  s->view = table_view(s->table);
+  XG_CUDA(cudaMalloc(&s->dst_global, max_edge * sizeof(uint32_t)));
+  XG_CUDA(cudaMalloc(&s->pos, max_edge * sizeof(uint32_t)));
+  XG_CUDA(cudaMalloc(&s->scan_mem, s->scan_bytes));
+  if (cfg->stream) {
+    s->stream = as_stream(cfg->stream);
+  } else {
+    XG_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    s->own_stream = true;
+  }
+  const char *env = std::getenv("XG_NO_GRAPH");
+  s->stage_timing = (cfg->flags & XG_SAMPLER_STAGE_TIMING) != 0;
+  s->use_graph = !(cfg->flags & (XG_SAMPLER_NO_GRAPH | XG_SAMPLER_STAGE_TIMING)) && !(env && env[0] == '1');
+  const uint32_t nslots = cfg->num_slots ? cfg->num_slots : 2;
+  for (uint32_t i = 0; i < nslots; ++i) {
+    xg_batch *b = nullptr;
+    if ((rc = alloc_slot(s, &b))) {
+      xg_sampler_destroy(s);
+      return rc;
+    }
+    b->index = (int)i;
+    s->slots.push_back(b);
+  }
+  *out = s;
+  return XG_OK;
+}
+
+int xg_sampler_destroy(xg_sampler *s) {
+  if (!s) return XG_OK;
+  DeviceScope scope(s->device);
+  if (s->stream) cudaStreamSynchronize(s->stream);
+  for (auto *b : s->slots) free_slot(b);
+  cudaFree(s->dst_global);
+  cudaFree(s->pos);
+  cudaFree(s->scan_mem);
+  if (s->table) xg_hashtable_destroy(s->table);
+  if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
+  delete s;
+  return XG_OK;
+}
+
+int xg_sampler_submit(xg_sampler *s, const uint32_t *seeds, size_t num_seeds, int seeds_on_device,
+                      uint64_t batch_key, xg_batch **out) {
+  XG_REQUIRE(s && out, "NULL argument");
+  XG_REQUIRE(seeds != nullptr || num_seeds == 0, "seeds is NULL");
+  XG_REQUIRE(num_seeds <= s->cfg.batch_size, "more seeds than batch_size");
+  DeviceScope scope(s->device);
+  std::lock_guard<std::mutex> lk(s->mu);
+  xg_batch *b = nullptr;
+  for (auto *c : s->slots) {
+    int expected = 0;
+    if (c->claimed.compare_exchange_strong(expected, 1)) {
+      b = c;
+      break;
+    }
+  }
+  if (!b) {
+    set_error("every batch slot is still held: release a batch (xg_batch_release) or raise num_slots");
+    return XG_ERR_CAPACITY;
+  }
+  cudaStream_t st = s->stream;
+  // the slot's pinned staging is about to be rewritten: its previous batch must have drained
+  if (b->recorded && cudaEventSynchronize(b->done) != cudaSuccess) {
+    b->claimed.store(0);
+    set_error("cudaEventSynchronize failed on a recycled batch slot");
+    return XG_ERR_CUDA;
+  }
+  if (s->dirty.exchange(false)) {  // after an overflow the targeted Reset cannot know every used slot
+    const size_t cap = (size_t)s->view.mask + 1;
+    if (cudaMemsetAsync(s->view.slots, 0xFF, cap * sizeof(uint2), st) != cudaSuccess ||
+        cudaMemsetAsync(s->view.items, 0, (kMaxFills + 2) * sizeof(uint32_t), st) != cudaSuccess) {
+      b->claimed.store(0);
+      return XG_ERR_CUDA;
+    }
+  }
+  b->key = batch_key;
+  b->num_seeds = (uint32_t)num_seeds;
+  b->h_params->num_seeds = num_seeds;
+  b->h_params->num_seeds32 = (uint32_t)num_seeds;
+  b->h_params->pad = 0;
+  b->h_params->rng_key = philox_key(s->cfg.seed, batch_key);
+  int rc = XG_OK;
+  auto fail = [&](int code) {
+    b->claimed.store(0);
+    return code;
+  };
+  if (num_seeds) {
+    if (seeds_on_device) {
+      if (cudaMemcpyAsync(b->seeds, seeds, num_seeds * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st) != cudaSuccess)
+        return fail(XG_ERR_CUDA);
+    } else {
+      std::memcpy(b->h_seeds, seeds, num_seeds * sizeof(uint32_t));
+      if (cudaMemcpyAsync(b->seeds, b->h_seeds, num_seeds * sizeof(uint32_t), cudaMemcpyHostToDevice, st) != cudaSuccess)
+        return fail(XG_ERR_CUDA);
+    }
+  }
+  if (cudaMemcpyAsync(b->d_params, b->h_params, sizeof(BatchParams), cudaMemcpyHostToDevice, st) != cudaSuccess)
+    return fail(XG_ERR_CUDA);
+
+  if (s->use_graph) {
+    if (!b->graph) {  // first use of this slot: record the chain once
+      const uint64_t before = g_launches.load();
+      cudaGraph_t g = nullptr;
+      if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+        set_error("cudaStreamBeginCapture failed");
+        return fail(XG_ERR_CUDA);
+      }
+      rc = enqueue_batch(s, b);
+      cudaError_t e = cudaStreamEndCapture(st, &g);
+      s->launches_per_batch = (uint32_t)(g_launches.load() - before);
+      g_launches.store(before);
+      if (rc || e != cudaSuccess || !g) {
+        if (!rc) set_error(std::string("graph capture failed: ") + cudaGetErrorString(e));
+        if (g) cudaGraphDestroy(g);
+        return fail(rc ? rc : XG_ERR_CUDA);
+      }
+      e = cudaGraphInstantiate(&b->graph, g, 0);
+      cudaGraphDestroy(g);
+      if (e != cudaSuccess) {
+        set_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
+        return fail(XG_ERR_CUDA);
+      }
+    }
+    if (cudaGraphLaunch(b->graph, st) != cudaSuccess) {
+      set_error(std::string("cudaGraphLaunch: ") + cudaGetErrorString(cudaGetLastError()));
+      return fail(XG_ERR_CUDA);
+    }
+    g_launches.fetch_add(s->launches_per_batch);
+  } else {
+    const uint64_t before = g_launches.load();
+    if ((rc = enqueue_batch(s, b))) return fail(rc);
+    s->launches_per_batch = (uint32_t)(g_launches.load() - before);
+  }
+  if (cudaEventRecord(b->done, st) != cudaSuccess) return fail(XG_ERR_CUDA);
+  b->recorded = true;
+  *out = b;
+  return XG_OK;
+}
+
+int xg_batch_wait(xg_batch *b, xg_batch_view *view) {
+  XG_REQUIRE(b && b->owner, "batch is NULL");
+  XG_REQUIRE(b->claimed.load() == 1, "batch is not in flight");
+  xg_sampler *s = b->owner;
+  DeviceScope scope(s->device);
+  XG_CUDA(cudaEventSynchronize(b->done));
+  const BatchCounts &c = *b->h_counts;
+  const int L = (int)s->cfg.num_layer;
+  bool over = c.overflow != 0;
+  for (int l = L - 1; l >= 0 && !over; --l) {
+    const int fill = (L - 1 - l) + 2;
+    if (l != L - 1 && c.items[fill - 1] > s->cap_in[l]) over = true;
+  }
+  if (c.items[L + 1] > s->cap_input) over = true;
+  if (over) {
+    s->dirty.store(true);
+    set_error("minibatch outgrew its buffers (max_input_nodes=" + std::to_string(s->cap_input) + ")");
+    return XG_ERR_CAPACITY;
+  }
+  if (!view) return XG_OK;
+  std::memset(view, 0, sizeof(*view));
+  view->key = b->key;
+  view->num_layer = (uint32_t)L;
+  view->num_output = b->num_seeds;
+  view->num_input = c.items[L + 1];
+  for (int l = L - 1; l >= 0; --l) {
+    const int fill = (L - 1 - l) + 2;
+    view->row[l] = b->row[l];
+    view->col[l] = b->col[l];
+    view->data[l] = nullptr;
+    view->num_dst[l] = (l == L - 1) ? b->num_seeds : c.items[fill - 1];  // num_dst = num_input (dist_loops.cc:304-306)
+    view->num_src[l] = c.items[fill];
+    view->num_edge[l] = c.num_edge[l];
+  }
+  view->input_nodes = b->input_nodes;
+  view->output_nodes = b->seeds;
+  view->input_feat = s->has_store ? b->feat : nullptr;
+  view->output_label = s->label ? b->label : nullptr;
+  return XG_OK;
+}
+
+int xg_batch_release(xg_batch *b) {
+  if (!b) return XG_OK;
+  b->claimed.store(0);
+  return XG_OK;
+}
+
+int xg_batch_stage_ms(xg_batch *b, int stage, int layer, float *ms) {
+  XG_REQUIRE(b && b->owner && ms, "NULL argument");
+  xg_sampler *s = b->owner;
+  XG_REQUIRE(s->stage_timing, "sampler was not created with XG_SAMPLER_STAGE_TIMING");
+  const int L = (int)s->cfg.num_layer;
+  int first;  // index of the mark that opens the stage
+  switch (stage) {
+    case XG_STAGE_RESET_SEEDS: first = 0; break;
+    case XG_STAGE_SAMPLE: case XG_STAGE_NUMBER: case XG_STAGE_REMAP:
+      XG_REQUIRE(layer >= 0 && layer < L, "layer out of range");
+      first = 1 + 3 * (L - 1 - layer) + (stage - XG_STAGE_SAMPLE);
+      break;
+    case XG_STAGE_INPUT_NODES: first = 1 + 3 * L; break;
+    case XG_STAGE_FEATURE: first = 2 + 3 * L; break;
+    case XG_STAGE_LABEL: first = 3 + 3 * L; break;
+    default: XG_REQUIRE(false, "unknown stage");
+  }
+  XG_REQUIRE(first + 1 < b->num_marks, "stage was not recorded");
+  DeviceScope scope(s->device);
+  XG_CUDA(cudaEventSynchronize(b->marks[first + 1]));
+  XG_CUDA(cudaEventElapsedTime(ms, b->marks[first], b->marks[first + 1]));
+  return XG_OK;
+}
+
+void *xg_sampler_stream(xg_sampler *s) { return s ? s->stream : nullptr; }
+uint32_t xg_sampler_launches_per_batch(xg_sampler *s) { return s ? s->launches_per_batch : 0; }
+
+}  // extern "C"

@@ -55,8 +55,8 @@ __global__ void __launch_bounds__(kSampleBlock)
 sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint32_t num_input_max,
                       const uint32_t *__restrict__ d_num_input, uint32_t fanout,
                       uint32_t *__restrict__ out_src, uint32_t *__restrict__ out_dst,
-                      uint64_t *__restrict__ d_num_out, uint2 rng_key, SampleFusion fusion,
-                      uint32_t *ticket, uint64_t *scan_state) {
+                      uint64_t *__restrict__ d_num_out, uint2 rng_key, const uint2 *__restrict__ d_rng_key,
+                      uint32_t salt, SampleFusion fusion, uint32_t *ticket, uint64_t *scan_state) {
   static_assert(kSampleBlock == kSampleTile, "phase A maps one thread to one node");
   __shared__ const uint32_t *s_edges[kSampleTile];
   __shared__ uint32_t s_deg[kSampleTile];
@@ -68,6 +68,7 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
 
   uint32_t n = d_num_input ? *d_num_input : num_input_max;
   if (n > num_input_max) n = num_input_max;
+  if (d_rng_key) rng_key = *d_rng_key;  // per-batch key lives on the device when the batch is a replayed graph
   const uint32_t num_tiles = (n + kSampleTile - 1) / kSampleTile;
   if (num_tiles == 0) {
     if (blockIdx.x == 0 && threadIdx.x == 0) *d_num_out = 0;
@@ -131,14 +132,14 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
         uint32_t draw[VPL];
         {
           const uint32_t node_pos = tile * kSampleTile + j;
-          const uint4 r = Philox::rand4(rng_key, make_uint4(node_pos, gl, 0x5A4D4752u, 0u));
+          const uint4 r = Philox::rand4(rng_key, make_uint4(node_pos, gl, salt, 0u));
           const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
           const uint32_t j0 = big ? (ndeg - fanout) : 0u;
 #pragma unroll
           for (int k = 0; k < VPL; ++k) {
             uint32_t rk = rr[k & 3];
             if (VPL > 4 && k >= 4) {  // more than four slots per lane: extra Philox blocks
-              const uint4 r2 = Philox::rand4(rng_key, make_uint4(node_pos, gl, 0x5A4D4752u, (uint32_t)(k >> 2)));
+              const uint4 r2 = Philox::rand4(rng_key, make_uint4(node_pos, gl, salt, (uint32_t)(k >> 2)));
               const uint32_t rr2[4] = {r2.x, r2.y, r2.z, r2.w};
               rk = rr2[k & 3];
             }
@@ -190,18 +191,18 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
 template <int G, int VPL>
 int launch_variant(const xg_graph &g, const uint32_t *d_input, size_t num_input_max,
                    const uint32_t *d_num_input, size_t fanout, uint32_t *d_out_src, uint32_t *d_out_dst,
-                   uint64_t *d_num_out, uint2 key, const SampleFusion &fusion, const ScanSpace &scan,
-                   cudaStream_t s) {
+                   uint64_t *d_num_out, uint2 key, const uint2 *d_key, uint32_t salt,
+                   const SampleFusion &fusion, const ScanSpace &scan, cudaStream_t s) {
   const size_t tiles = (num_input_max + kSampleTile - 1) / kSampleTile;
   const unsigned grid = grid_for(tiles, 6);
   if (fusion.enabled) {
     sample_uniform_kernel<G, VPL, true><<<grid, kSampleBlock, 0, s>>>(
         g, d_input, (uint32_t)num_input_max, d_num_input, (uint32_t)fanout, d_out_src, d_out_dst,
-        d_num_out, key, fusion, scan.ticket, scan.state);
+        d_num_out, key, d_key, salt, fusion, scan.ticket, scan.state);
   } else {
     sample_uniform_kernel<G, VPL, false><<<grid, kSampleBlock, 0, s>>>(
         g, d_input, (uint32_t)num_input_max, d_num_input, (uint32_t)fanout, d_out_src, d_out_dst,
-        d_num_out, key, fusion, scan.ticket, scan.state);
+        d_num_out, key, d_key, salt, fusion, scan.ticket, scan.state);
   }
   XG_LAUNCHED();
   return XG_OK;
@@ -212,7 +213,8 @@ int launch_variant(const xg_graph &g, const uint32_t *d_input, size_t num_input_
 int launch_sample_uniform(const xg_graph &g, const uint32_t *d_input, size_t num_input_max,
                           const uint32_t *d_num_input, size_t fanout, uint32_t *d_out_src,
                           uint32_t *d_out_dst, uint64_t *d_num_out, uint64_t seed, uint64_t batch_key,
-                          const SampleFusion &fusion, const ScanSpace &scan, cudaStream_t s) {
+                          const uint2 *d_rng_key, uint32_t salt, const SampleFusion &fusion,
+                          const ScanSpace &scan, cudaStream_t s) {
   XG_REQUIRE(fanout >= 1 && fanout <= 512, "fanout must be in [1, 512]");
   XG_REQUIRE(num_input_max < (1ull << 31), "too many input nodes");
   XG_REQUIRE(num_input_max * fanout < (1ull << 31), "num_input * fanout must stay below 2^31");
@@ -222,11 +224,10 @@ int launch_sample_uniform(const xg_graph &g, const uint32_t *d_input, size_t num
     XG_CUDA(cudaMemsetAsync(d_num_out, 0, sizeof(uint64_t), s));
     return XG_OK;
   }
-  const uint64_t k64 = seed ^ (batch_key * 0x9E3779B97F4A7C15ull + 0x7F4A7C15F39CC060ull);
-  const uint2 key = make_uint2((uint32_t)k64, (uint32_t)(k64 >> 32));
+  const uint2 key = philox_key(seed, batch_key);
 #define XG_SAMPLE(G, VPL)                                                                         \
   return launch_variant<G, VPL>(g, d_input, num_input_max, d_num_input, fanout, d_out_src, d_out_dst, \
-                                d_num_out, key, fusion, scan, s)
+                                d_num_out, key, d_rng_key, salt, fusion, scan, s)
   if (fanout <= 4) XG_SAMPLE(4, 1);
   if (fanout <= 8) XG_SAMPLE(8, 1);
   if (fanout <= 16) XG_SAMPLE(16, 1);
@@ -283,5 +284,6 @@ extern "C" int xg_sample_khop(const xg_graph *g, int sample_type, const uint32_t
   none.enabled = false;
   static_assert(sizeof(size_t) == sizeof(uint64_t), "size_t must be 64-bit");
   return launch_sample_uniform(*g, d_input, num_input, nullptr, fanout, d_out_src, d_out_dst,
-                               reinterpret_cast<uint64_t *>(d_num_out), seed, batch_key, none, scan, s);
+                               reinterpret_cast<uint64_t *>(d_num_out), seed, batch_key, nullptr, kSampleSalt, none,
+                               scan, s);
 }

@@ -1,0 +1,150 @@
+"""Synthetic GGMS stores of the BASELINE.json shapes, built directly in HBM.
+
+Host-side mirror of what DistGraph::GraphLoad / FeatureLoad and the GPUCacheManager constructor leave
+behind (cuda/dist_graph.cu:309-547, cuda/cuda_cache_manager_host.cc:133-254): per-GPU topology
+partitions (node v -> part v % P, row v / P), feature-cache partitions (cache rank r -> part r % P,
+row r / P), and the direct-address cache table u32[V].  The data itself comes from the device-side
+generator (csrc/synth.cu); torch only owns the memory.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import ops
+from ._clib import check, lib
+
+# name -> (num_node, target num_edge, feat dim, feat dtype, num_class, train fraction)
+SHAPES = {
+    "products": (2_449_029, 61_859_140, 100, torch.float32, 47, 0.08),
+    "papers100M": (111_059_956, 1_615_685_872, 128, torch.float32, 172, 0.0109),
+    "twitter": (41_652_230, 1_468_365_182, 256, torch.float32, 150, 0.01),
+    "friendster": (65_608_366, 3_612_134_270, 128, torch.float32, 100, 0.01),
+    "mag240M-homo": (244_160_499, 1_728_364_232, 768, torch.float16, 153, 0.0045),
+}
+SYNTH_SEED = 0x5A4D47524150
+
+
+def degree_constant(num_node: int, num_edge: int) -> float:
+    """c of degree(v) = floor(c * sqrt(V / (v + 1))): sum over v ~= 2 c V - V/2 (floor loses ~1/2 each)."""
+    return (num_edge + 0.5 * num_node) / (2.0 * num_node)
+
+
+def train_set(num_node: int, count: int) -> np.ndarray:
+    """`count` distinct node ids spread over the whole id range (multiplicative walk, gcd(K, V) = 1)."""
+    K = 2654435761  # prime
+    assert num_node % K != 0
+    i = np.arange(count, dtype=np.uint64)
+    return ((i * np.uint64(K) + np.uint64(12345)) % np.uint64(num_node)).astype(np.uint32)
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def gen_degrees(begin: int, stride: int, n: int, num_node: int, c: float, device, max_deg: int = 0xFFFFFFFF):
+    deg = torch.empty(n, dtype=torch.int32, device=device)
+    check(lib.xg_synth_degrees(deg.data_ptr(), begin, stride, n, num_node, c, max_deg, _stream()))
+    return deg
+
+
+def gen_csr(begin: int, stride: int, n: int, num_node: int, c: float, seed: int, device, max_deg: int = 0xFFFFFFFF):
+    """(indptr u32[n+1], indices u32[E]) of nodes begin, begin+stride, ... as int32 views."""
+    deg = gen_degrees(begin, stride, n, num_node, c, device, max_deg)
+    indptr64 = torch.zeros(n + 1, dtype=torch.int64, device=device)
+    torch.cumsum(deg, 0, out=indptr64[1:])
+    num_edge = int(indptr64[-1].item())
+    assert num_edge < (1 << 32), "edge offsets are 32-bit (IdType)"
+    indptr = indptr64.to(torch.int32)  # wraps: the bits are the uint32 offsets
+    del indptr64, deg
+    indices = torch.empty(max(num_edge, 1), dtype=torch.int32, device=device)
+    check(lib.xg_synth_indices(indices.data_ptr(), indptr.data_ptr(), begin, stride, n, num_node, seed, _stream()))
+    return indptr, indices, num_edge
+
+
+def gen_features(n_rows: int, dim: int, dtype, device, *, row_ids=None, begin: int = 0, stride: int = 1):
+    out = torch.empty((n_rows, dim), dtype=dtype, device=device)
+    code = 0 if dtype == torch.float32 else 2
+    check(lib.xg_synth_features(out.data_ptr(), None if row_ids is None else row_ids.data_ptr(), begin, stride,
+                                n_rows, dim, code, _stream()))
+    return out
+
+
+@dataclass
+class GGMSStore:
+    """What one GPU holds after sample_init + train_init (dist_engine.cc:198-244, 589-700)."""
+    num_node: int
+    num_edge: int
+    dim: int
+    dtype: torch.dtype
+    num_class: int
+    rank: int
+    world: int
+    graph: object = None           # XgGraph handle (by-value pointers: local + peer parts)
+    store: object = None           # XgFeatureStore handle
+    label: torch.Tensor = None     # int64[V] on the device
+    train: np.ndarray = None       # whole train set (host, uint32)
+    local: dict = field(default_factory=dict)  # tensors this GPU owns
+
+    @property
+    def row_bytes(self) -> int:
+        return self.dim * torch.empty((), dtype=self.dtype).element_size()
+
+
+def cache_rank_nodes(num_node: int, num_cached: int) -> np.ndarray:
+    """The cached set in cache-rank order: first `num_cached` entries of the degree ranking (for the
+    synthetic shapes degree is non-increasing in the id, so the stable ranking is the identity),
+    shuffled as GPUCacheManager does (std::shuffle with mt19937(num_cached),
+    cuda_cache_manager_host.cc:162-171) so that rank r -> part r % P is load balanced."""
+    nodes = np.arange(num_cached, dtype=np.uint32)
+    check(lib.xg_shuffle_cache_ranks(nodes.ctypes.data, num_cached))
+    return nodes
+
+
+def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale: int = 1, cache_pct: float = 1.0,
+                with_features: bool = True, seed: int = SYNTH_SEED) -> GGMSStore:
+    """Generate THIS rank's shards (topology part `rank`, feature part `rank`) of the named shape,
+    scaled down by `scale`. Peer parts are attached afterwards (attach_peers) from IPC handles."""
+    V, E, dim, dtype, num_class, train_frac = SHAPES[shape]
+    V, E = V // scale, E // scale
+    dev = torch.device("cuda", device)
+    c = degree_constant(V, E)
+    P = world
+    st = GGMSStore(num_node=V, num_edge=0, dim=dim, dtype=dtype, num_class=num_class, rank=rank, world=world)
+    with torch.cuda.device(dev):
+        # topology: use_dist_graph = 1.0 -> num_cache_node = V, every node lives in some GPU part
+        n_part = (V - rank + P - 1) // P
+        indptr, indices, ne = gen_csr(rank, P, n_part, V, c, seed, dev)
+        st.local.update(indptr=indptr, indices=indices, num_local_edge=ne)
+        st.label = (torch.arange(V, dtype=torch.int64, device=dev) % num_class)
+        if with_features:
+            n_cached = int(V * cache_pct)
+            ranks = cache_rank_nodes(V, n_cached)
+            table = np.full(V, 0xFFFFFFFF, np.uint32)
+            table[ranks] = np.arange(n_cached, dtype=np.uint32)
+            st.local["cache_table"] = torch.from_numpy(table.view(np.int32)).to(dev)
+            mine = torch.from_numpy(np.ascontiguousarray(ranks[rank::P]).view(np.int32)).to(dev)
+            st.local["feat_part"] = gen_features(mine.numel(), dim, dtype, dev, row_ids=mine)
+            st.local["num_cached"] = n_cached
+            del mine
+        torch.cuda.synchronize()
+    st.train = train_set(V, max(1, int(V * train_frac)))
+    return st
+
+
+def attach(st: GGMSStore, part_indptr=None, part_indices=None, feat_parts=None, host_feat=None) -> GGMSStore:
+    """Fill the by-value handles. With world == 1 the local shards are the whole store; otherwise the
+    caller passes every part's pointer (local tensor or IPC-mapped peer address) in part order."""
+    P = st.world
+    if part_indptr is None:
+        assert P == 1
+        part_indptr, part_indices = [st.local["indptr"]], [st.local["indices"]]
+        feat_parts = [st.local.get("feat_part")]
+    st.graph = ops.make_graph(part_indptr=part_indptr, part_indices=part_indices, num_cache_node=st.num_node,
+                              num_node=st.num_node, host_indptr=None, host_indices=None)
+    if st.local.get("cache_table") is not None:
+        st.store = ops.make_feature_store(st.row_bytes, host_feat, st.local["cache_table"], parts=feat_parts,
+                                          local_parts=(st.rank,))
+    return st

@@ -222,3 +222,150 @@ def CombineCacheData(out: torch.Tensor, store: XgFeatureStore, cache_src, cache_
 
 def launch_count() -> int:
     return int(lib.xg_launch_count())
+
+
+# ------------------------------------------------------------------------------------------------
+# Minibatch engine: DoGPUSample + extract stage functions as one replayed CUDA graph (pipeline.cu)
+# ------------------------------------------------------------------------------------------------
+_TORCH_OF_CODE = {0: torch.float32, 1: torch.float64, 2: torch.float16, 3: torch.uint8, 4: torch.int32,
+                  5: torch.int8, 6: torch.int64}
+
+
+class _DevMem:
+    """__cuda_array_interface__ view of memory owned by a batch slot (keeps the batch alive)."""
+
+    def __init__(self, ptr: int, shape, typestr: str, owner):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (ptr, False),
+                                         "version": 3, "strides": None}
+        self._owner = owner
+
+
+_TYPESTR = {torch.float32: "<f4", torch.float64: "<f8", torch.float16: "<f2", torch.uint8: "|u1",
+            torch.int32: "<i4", torch.int8: "|i1", torch.int64: "<i8"}
+
+
+class Minibatch:
+    """One finished Task (common.h:246-285): zero-copy torch views of the batch slot's buffers, as
+    samgraph/torch/adapter.cc:62-134 hands them out (ids as int32). The slot is released when this
+    object dies (or on release())."""
+
+    def __init__(self, sampler: "MinibatchSampler", handle: c_void_p, view: _clib.XgBatchView):
+        self._sampler, self._h, self.view = sampler, handle, view
+        self.key = view.key
+        self.num_layer = view.num_layer
+        self.num_src = [int(view.num_src[l]) for l in range(self.num_layer)]
+        self.num_dst = [int(view.num_dst[l]) for l in range(self.num_layer)]
+        self.num_edge = [int(view.num_edge[l]) for l in range(self.num_layer)]
+        self.num_input, self.num_output = int(view.num_input), int(view.num_output)
+
+    def _t(self, ptr, shape, dtype):
+        n = 1
+        for s in shape:
+            n *= s
+        if n == 0 or not ptr:
+            return torch.empty(shape, dtype=dtype, device=self._sampler.device)
+        return torch.as_tensor(_DevMem(ptr, shape, _TYPESTR[dtype], self), device=self._sampler.device)
+
+    def row(self, l):
+        return self._t(self.view.row[l], (self.num_edge[l],), torch.int32)
+
+    def col(self, l):
+        return self._t(self.view.col[l], (self.num_edge[l],), torch.int32)
+
+    @property
+    def input_nodes(self):
+        return self._t(self.view.input_nodes, (self.num_input,), torch.int32)
+
+    @property
+    def output_nodes(self):
+        return self._t(self.view.output_nodes, (self.num_output,), torch.int32)
+
+    @property
+    def feat(self):
+        s = self._sampler
+        return self._t(self.view.input_feat, (self.num_input, s.feat_dim), s.feat_dtype) if self.view.input_feat else None
+
+    @property
+    def label(self):
+        return self._t(self.view.output_label, (self.num_output,), torch.int64) if self.view.output_label else None
+
+    def release(self):
+        if self._h is not None:
+            lib.xg_batch_release(self._h)
+            self._h = None
+
+    def __del__(self):
+        self.release()
+
+
+class MinibatchSampler:
+    """dist::DoGPUSample + DoGPULabelExtract + DoArch6GetCacheMissIndex + DoArch6GPUCacheFeatureCopy
+    (dist/dist_loops.cc) for one sampler GPU."""
+
+    def __init__(self, graph: XgGraph, fanout, batch_size: int, *, store: XgFeatureStore | None = None,
+                 feat_dim: int = 0, feat_dtype: torch.dtype = torch.float32, label: torch.Tensor | int | None = None,
+                 sample_type: int = kKHop0, seed: int = 0, num_slots: int = 2, max_input_nodes: int = 0,
+                 device: int = 0, use_graph: bool = True, stream: torch.cuda.Stream | None = None,
+                 stage_timing: bool = False):
+        cfg = _clib.XgSamplerConfig()
+        cfg.num_layer = len(fanout)
+        for i, f in enumerate(fanout):
+            cfg.fanout[i] = int(f)
+        cfg.batch_size = batch_size
+        cfg.sample_type = sample_type
+        cfg.num_slots = num_slots
+        cfg.flags = (0 if use_graph else 1) | (2 if stage_timing else 0)
+        cfg.feat_dim = feat_dim
+        cfg.feat_dtype = _DTYPE_CODE[feat_dtype]
+        cfg.seed = seed
+        cfg.max_input_nodes = max_input_nodes
+        cfg.stream = stream.cuda_stream if stream is not None else None
+        self.device = torch.device("cuda", device)
+        self.feat_dim, self.feat_dtype = feat_dim, feat_dtype
+        self._keep = [graph, store, label, stream]
+        h = c_void_p()
+        lp = label if isinstance(label, int) or label is None else label.data_ptr()
+        check(lib.xg_sampler_create(byref(h), byref(graph), byref(store) if store is not None else None, lp,
+                                    byref(cfg), device))
+        self._h = h
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib.xg_sampler_destroy(self._h)
+            self._h = None
+
+    def submit(self, seeds, batch_key: int = 0) -> c_void_p:
+        """Enqueue one minibatch; `seeds` is a host uint32 numpy array / CPU int32 tensor, or a CUDA int32
+        tensor. Returns the in-flight handle for wait()."""
+        b = c_void_p()
+        if isinstance(seeds, torch.Tensor):
+            on_dev = 1 if seeds.is_cuda else 0
+            ptr, n = seeds.data_ptr(), seeds.numel()
+        else:
+            on_dev, ptr, n = 0, seeds.ctypes.data, len(seeds)
+        check(lib.xg_sampler_submit(self._h, ptr, n, on_dev, batch_key, byref(b)))
+        return b
+
+    def wait(self, handle: c_void_p) -> Minibatch:
+        view = _clib.XgBatchView()
+        rc = lib.xg_batch_wait(handle, byref(view))
+        if rc != 0:
+            lib.xg_batch_release(handle)
+            check(rc)
+        return Minibatch(self, handle, view)
+
+    def sample(self, seeds, batch_key: int = 0) -> Minibatch:
+        return self.wait(self.submit(seeds, batch_key))
+
+    @property
+    def launches_per_batch(self) -> int:
+        return int(lib.xg_sampler_launches_per_batch(self._h))
+
+    @property
+    def stream_ptr(self) -> int:
+        return int(lib.xg_sampler_stream(self._h) or 0)
+
+
+def predict_num_nodes(batch_size: int, fanout) -> int:
+    arr = (c_uint32 * len(fanout))(*[int(f) for f in fanout])
+    return int(lib.xg_predict_num_nodes(batch_size, arr, len(fanout)))
