@@ -8,14 +8,14 @@
 // i.e. classification into index lists (with two scans and two D2H counts) followed by two
 // element-wise gathers whose routing (`% P`, `/ P`, pointer-table load) is redone per ELEMENT.
 //
-// Here: ONE launch.  A CTA takes a tile of rows;
-//   phase 1 (thread per row): node id -> cache_table -> (part, row) or host -> source row pointer,
-//            staged in shared memory -- the three dependent loads are issued for a whole tile at once;
-//   phase 2 (all threads): the tile is a flat list of 16-byte chunks (row-major), copied with
-//            8 independent 128-bit loads in flight per thread before the matching stores, so lanes
-//            are never idle on rows that are not a multiple of 512 B (e.g. 100 x fp32 = 25 chunks).
+// Here: ONE launch, warp-autonomous (see gather_rows_kernel): lane i of a warp resolves row i of a
+// 32-row group (node id -> cache_table -> (part, row) or host -> source pointer), then the warp copies the
+// group as a flat list of 16-byte chunks with 8 independent 128-bit loads in flight per lane, so lanes
+// are never idle on rows that are not a multiple of 512 B (e.g. 100 x fp32 = 25 chunks).
 // Local HBM, NVLink-peer HBM and pinned host rows take the same path; only the pointer differs.
 #include "extract.cuh"
+
+#include <cstdlib>
 
 namespace xg {
 
@@ -23,8 +23,6 @@ namespace {
 
 constexpr int kGatherBlock = 256;
 constexpr int kGatherUnroll = 8;
-constexpr int kGatherChunksPerTile = kGatherBlock * kGatherUnroll;  // 2048 chunks (32 KB at 16 B)
-constexpr int kGatherMaxRows = 256;                                  // rows per tile upper bound
 
 template <int VW> struct Vec;
 template <> struct Vec<16> { using T = int4; };
@@ -65,57 +63,109 @@ __device__ __forceinline__ const char *route_row(const xg_feature_store &st, int
   return static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
 }
 
-template <int VW>
-__global__ void __launch_bounds__(kGatherBlock)
+// One warp owns 32 consecutive rows at a time (a "group"); nothing in the kernel crosses a warp, so
+// there is no shared memory and no __syncthreads (the first version staged a CTA tile's row pointers in
+// shared memory and lost 40 % of its stall cycles on the barriers around that, ncu r01).
+//   lane i resolves row i of the group: index -> cache_table -> (part, row) | host -> source pointer;
+//   the 32 rows are then one flat list of 16-byte chunks (chunk f -> row f / cpr, col f % cpr), copied
+//   with kGatherUnroll independent 128-bit loads in flight per lane before the matching stores; the
+//   source / destination row pointers travel by warp shuffle.
+// The index and cache-table loads of the NEXT groups are issued before the current group is copied
+// (two-deep software pipeline), so the dependent index -> rank -> row chain never stalls the copy.
+template <int VW, int U, int MINB>
+__global__ void __launch_bounds__(kGatherBlock, MINB)
 gather_rows_kernel(const xg_feature_store st, int mode, const uint32_t *__restrict__ src_idx,
                    const uint32_t *__restrict__ dst_idx, size_t num_rows_max,
-                   const uint32_t *__restrict__ d_num_rows, uint32_t rows_per_tile,
-                   uint32_t chunks_per_row, char *__restrict__ out, unsigned long long *stats) {
+                   const uint32_t *__restrict__ d_num_rows, uint32_t cpr /* chunks per row */,
+                   char *__restrict__ out, unsigned long long *stats) {
   using V = typename Vec<VW>::T;
-  __shared__ const char *s_src[kGatherMaxRows];
-  __shared__ char *s_dst[kGatherMaxRows];
-  __shared__ unsigned s_class[3];
+  uint32_t num_rows = (uint32_t)num_rows_max;  // launch_gather checks num_rows_max < 2^32 - 2^20
+  if (d_num_rows && *d_num_rows < num_rows) num_rows = *d_num_rows;  // count still on the device
+  const unsigned lane = threadIdx.x & 31;
+  const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t num_warps = (gridDim.x * blockDim.x) >> 5;
+  const uint32_t num_groups = (num_rows + 31) / 32;
+  const uint32_t q = 32u / cpr, rem = 32u % cpr;  // chunk f + 32 -> (row + q, col + rem) with one carry
+  const bool by_table = (mode == kByNode) && st.cache_table != nullptr;
 
-  size_t num_rows = num_rows_max;
-  if (d_num_rows && *d_num_rows < num_rows_max) num_rows = *d_num_rows;  // count still on the device
-  const size_t num_tiles = (num_rows + rows_per_tile - 1) / rows_per_tile;
-  for (size_t tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-    const size_t row0 = tile * rows_per_tile;
-    const uint32_t rows = (uint32_t)((num_rows - row0) < rows_per_tile ? (num_rows - row0) : rows_per_tile);
-    if (stats && threadIdx.x < 3) s_class[threadIdx.x] = 0;
-    if (stats) __syncthreads();
-    // phase 1: resolve source / destination row pointers
-    if (threadIdx.x < rows) {
-      const size_t r = row0 + threadIdx.x;
-      int klass;
-      s_src[threadIdx.x] = route_row(st, mode, src_idx[r], &klass);
-      const size_t drow = dst_idx ? (size_t)dst_idx[r] : r;
-      s_dst[threadIdx.x] = out + drow * st.row_bytes;
-      if (stats) atomicAdd(&s_class[klass], 1u);
+  // pipeline registers: idx of group g+1 (arrived or in flight), rank of group g
+  uint32_t g = warp;
+  uint32_t idx_cur = 0, rank_cur = kEmpty, idx_nxt = 0;
+  if (g < num_groups) {
+    const uint32_t r = g * 32 + lane;
+    if (r < num_rows) {
+      idx_cur = src_idx[r];
+      if (by_table) rank_cur = __ldg(st.cache_table + idx_cur);
     }
-    __syncthreads();
-    if (stats && threadIdx.x < 3 && s_class[threadIdx.x])
-      atomicAdd(stats + threadIdx.x, (unsigned long long)s_class[threadIdx.x]);
-
-    // phase 2: flat chunk copy, kGatherUnroll loads in flight per thread
-    const uint32_t total = rows * chunks_per_row;
-    for (uint32_t f0 = 0; f0 < total; f0 += kGatherChunksPerTile) {
-      V buf[kGatherUnroll];
-      uint32_t row[kGatherUnroll], col[kGatherUnroll];
+    const uint64_t rn = (uint64_t)(g + num_warps) * 32 + lane;
+    if (rn < num_rows) idx_nxt = src_idx[rn];
+  }
+  for (; g < num_groups; g += num_warps) {
+    const uint32_t row0 = g * 32;
+    const uint32_t rows = (num_rows - row0) < 32 ? (num_rows - row0) : 32;
+    // ---- issue the look-ahead loads: rank of group g+1, index of group g+2 ----
+    uint32_t rank_nxt = kEmpty, idx_nn = 0;
+    {
+      const uint64_t rn = (uint64_t)(g + num_warps) * 32 + lane;
+      if (by_table && rn < num_rows) rank_nxt = __ldg(st.cache_table + idx_nxt);
+      const uint64_t rnn = ((uint64_t)g + 2ull * num_warps) * 32 + lane;
+      if (rnn < num_rows) idx_nn = src_idx[rnn];
+    }
+    // ---- route my row ----
+    const char *sp = nullptr;
+    char *dp = nullptr;
+    int klass = 2;
+    if (lane < rows) {
+      uint32_t rank = kEmpty;
+      if (mode == kCacheRank) rank = idx_cur;
+      else if (by_table) rank = rank_cur;
+      if (rank == kEmpty) {
+        sp = static_cast<const char *>(st.host) + (size_t)idx_cur * st.row_bytes;
+      } else {
+        const uint32_t part = rank % st.num_part;
+        klass = ((st.local_part_mask >> part) & 1u) ? 0 : 1;
+        sp = static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
+      }
+      const size_t drow = dst_idx ? (size_t)dst_idx[row0 + lane] : row0 + lane;
+      dp = out + drow * st.row_bytes;
+    }
+    if (stats) {
 #pragma unroll
-      for (int u = 0; u < kGatherUnroll; ++u) {
-        const uint32_t f = f0 + u * kGatherBlock + threadIdx.x;
-        row[u] = f / chunks_per_row;
-        col[u] = f - row[u] * chunks_per_row;
-        if (f < total) buf[u] = ld_stream(reinterpret_cast<const V *>(s_src[row[u]]) + col[u]);
+      for (int c = 0; c < 3; ++c) {
+        const unsigned m = __ballot_sync(0xffffffffu, lane < rows && klass == c);
+        if (lane == 0 && m) atomicAdd(stats + c, (unsigned long long)__popc(m));
+      }
+    }
+    // ---- flat chunk copy ----
+    const uint32_t total = rows * cpr;
+    uint32_t row = lane / cpr, col = lane - row * cpr;  // chunk `lane`
+    for (uint32_t f0 = 0; f0 < total; f0 += 32 * U) {
+      V buf[U];
+      uint32_t lrow = row, lcol = col;  // the load loop walks a copy; the store loop re-walks (fewer registers)
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const uint32_t f = f0 + u * 32 + lane;
+        const unsigned long long s64 =
+            __shfl_sync(0xffffffffu, (unsigned long long)reinterpret_cast<uintptr_t>(sp), lrow & 31);
+        if (f < total) buf[u] = ld_stream(reinterpret_cast<const V *>(s64) + lcol);
+        lrow += q;
+        lcol += rem;
+        if (lcol >= cpr) { lcol -= cpr; ++lrow; }
       }
 #pragma unroll
-      for (int u = 0; u < kGatherUnroll; ++u) {
-        const uint32_t f = f0 + u * kGatherBlock + threadIdx.x;
-        if (f < total) st_stream(reinterpret_cast<V *>(s_dst[row[u]]) + col[u], buf[u]);
+      for (int u = 0; u < U; ++u) {
+        const uint32_t f = f0 + u * 32 + lane;
+        const unsigned long long d64 =
+            __shfl_sync(0xffffffffu, (unsigned long long)reinterpret_cast<uintptr_t>(dp), row & 31);
+        if (f < total) st_stream(reinterpret_cast<V *>(d64) + col, buf[u]);
+        row += q;
+        col += rem;
+        if (col >= cpr) { col -= cpr; ++row; }
       }
     }
-    __syncthreads();  // pointer staging is reused by the next tile
+    idx_cur = idx_nxt;
+    rank_cur = rank_nxt;
+    idx_nxt = idx_nn;
   }
 }
 
@@ -138,26 +188,38 @@ int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx,
   XG_REQUIRE(st.row_bytes > 0, "row_bytes is 0");
   XG_REQUIRE(out != nullptr && src_idx != nullptr, "NULL buffer");
   XG_REQUIRE(st.num_part <= XG_MAX_PARTS, "too many partitions");
+  XG_REQUIRE(num_rows < 0xFFF00000ull, "too many rows for one launch");
   XG_REQUIRE(mode != kCacheRank || st.num_part > 0, "cache-rank gather needs a partitioned cache");
   XG_REQUIRE(mode == kCacheRank || st.host != nullptr || st.cache_table != nullptr, "no source table");
   const int vw = pick_vector_width(st, out);
   const uint64_t cpr64 = st.row_bytes / vw;
   XG_REQUIRE(cpr64 < (1u << 24), "row too long");
   const uint32_t cpr = (uint32_t)cpr64;
-  uint32_t rows_per_tile = kGatherChunksPerTile / cpr;
-  if (rows_per_tile < 1) rows_per_tile = 1;
-  if (rows_per_tile > kGatherMaxRows) rows_per_tile = kGatherMaxRows;
-  const size_t tiles = (num_rows + rows_per_tile - 1) / rows_per_tile;
-  const unsigned grid = grid_for(tiles, 8);
+  // one warp per 32-row group, grid-stride; 8 CTAs of 256 threads per SM when registers allow
+  const size_t groups = (num_rows + 31) / 32;
+  const size_t ctas = (groups + kGatherBlock / 32 - 1) / (kGatherBlock / 32);
   auto *o = static_cast<char *>(out);
   auto *st64 = reinterpret_cast<unsigned long long *>(stats);
+#define XG_GATHER(VW, U, MINB)                                                                       \
+  gather_rows_kernel<VW, U, MINB><<<grid_for(ctas, MINB), kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, \
+                                                                               num_rows, d_num_rows, cpr, o, st64)
+  static const int variant = [] {
+    const char *e = std::getenv("XG_GATHER_VARIANT");
+    return e ? std::atoi(e) : 0;
+  }();
   switch (vw) {
-    case 16: gather_rows_kernel<16><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
-    case 8: gather_rows_kernel<8><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
-    case 4: gather_rows_kernel<4><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
-    case 2: gather_rows_kernel<2><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
-    default: gather_rows_kernel<1><<<grid, kGatherBlock, 0, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rows_per_tile, cpr, o, st64); break;
+    case 16:
+      // measured on B200 (papers100M-shape batch, 4.9 M x 512 B rows): U=4/4 CTAs 0.925 ms, U=8/2 CTAs 0.920,
+      // U=8/3 CTAs 0.933 (spills), U=6/4 0.951 (spills), U=4/6 0.983 (spills); r01 shared-memory version 1.050
+      if (variant == 1) XG_GATHER(16, 8, 2);
+      else XG_GATHER(16, 4, 4);
+      break;
+    case 8: XG_GATHER(8, 8, 3); break;
+    case 4: XG_GATHER(4, 8, 3); break;
+    case 2: XG_GATHER(2, 8, 3); break;
+    default: XG_GATHER(1, 8, 3); break;
   }
+#undef XG_GATHER
   XG_LAUNCHED();
   return XG_OK;
 }

@@ -136,14 +136,25 @@ table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, size_t n_max,
   }
 }
 
-// Targeted Reset: free exactly the slots the finished batch numbered (the reference bumps a
-// version word instead, cuda_hashtable.cu:739-742; 8-byte slots have no room for one).
+// Reset.  The reference bumps a version word (cuda_hashtable.cu:739-742); 8-byte slots have no room for
+// one.  Two ways, chosen on the device from the number of ids the finished batch numbered:
+//   few ids  -> free exactly those slots (one scattered 8-byte store per id, n2o_slot remembers where);
+//   many ids -> stream 0xFF over the whole table with 16-byte stores: cap * 8 bytes at copy bandwidth
+//               beats one random sector per id, and it leaves the (L2-sized) table resident in L2 for
+//               the inserts that follow.
 __global__ void __launch_bounds__(256)
 table_clear_kernel(TableView t, int fill) {
   const uint32_t n = min(t.items[fill], t.n2o_cap);
-  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n;
-       i += (uint64_t)gridDim.x * blockDim.x)
-    t.slots[t.n2o_slot[i]] = make_uint2(kEmpty, kEmpty);
+  const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  const uint64_t nthr = (uint64_t)gridDim.x * blockDim.x;
+  if ((uint64_t)n * 8 >= t.cap) {
+    uint4 *p = reinterpret_cast<uint4 *>(t.slots);
+    const uint64_t n4 = t.cap / 2;  // cap is even
+    const uint4 free4 = make_uint4(kEmpty, kEmpty, kEmpty, kEmpty);
+    for (uint64_t i = tid; i < n4; i += nthr) p[i] = free4;
+  } else {
+    for (uint64_t i = tid; i < n; i += nthr) t.slots[t.n2o_slot[i]] = make_uint2(kEmpty, kEmpty);
+  }
 }
 
 __global__ void __launch_bounds__(256)
@@ -192,7 +203,7 @@ int launch_table_assign(const TableView &t, const uint32_t *pos, size_t n_max, c
 
 int launch_table_clear(const TableView &t, int fill, size_t max_items, cudaStream_t s) {
   if (fill > 0) {
-    table_clear_kernel<<<grid_for((max_items + 255) / 256, 8), 256, 0, s>>>(t, fill);
+    table_clear_kernel<<<grid_for((max_items + 255) / 256, 8), 256, 0, s>>>(t, fill);  // 8 x 256 thr = full SM
     XG_LAUNCHED();
   }
   XG_CUDA(cudaMemsetAsync(t.items, 0, (kMaxFills + 2) * sizeof(uint32_t), s));
@@ -229,12 +240,6 @@ struct xg_hashtable {
 };
 
 namespace {
-
-size_t next_pow2(size_t n) {
-  size_t c = 1024;
-  while (c < n) c <<= 1;
-  return c;
-}
 
 struct DeviceGuard {
   int prev = 0;
@@ -333,18 +338,21 @@ int xg_hashtable_create(xg_hashtable **out, size_t max_items, int device) {
   auto *t = new xg_hashtable();
   t->device = device;
   t->max_items = max_items;
-  // slots per item: 2.0 by default (the reference's scale, cuda_hashtable.cu:146-149); XG_TABLE_LOAD_PCT
-  // trades probe length for footprint (a table that stays inside the 126 MB L2 probes much faster)
-  size_t pct = 200;
+  // slots per item: 1.25 by default.  The reference takes 2-4 (cuda_hashtable.cu:146-149) in 16-byte
+  // buckets; here the worst-case batch of the headline config (8.45 M ids) must stay inside the 126 MB
+  // L2 (84 MB at 1.25), because every probe is a random access and an L2 hit costs a third of a DRAM
+  // miss.  A typical batch fills 45 % of that.  XG_TABLE_SLOTS_PCT overrides (>= 110).
+  size_t pct = 125;
   if (const char *e = std::getenv("XG_TABLE_SLOTS_PCT")) pct = std::strtoul(e, nullptr, 10);
   if (pct < 110) pct = 110;
-  t->capacity = next_pow2(max_items * pct / 100);
+  t->capacity = (max_items * pct / 100 + 1024) & ~(size_t)1;
+  XG_REQUIRE(t->capacity < (1ull << 32), "table too large");
   XG_CUDA(cudaMalloc(&t->view.slots, t->capacity * sizeof(uint2)));
   XG_CUDA(cudaMalloc(&t->view.n2o, max_items * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&t->view.n2o_slot, max_items * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&t->view.items, (kMaxFills + 2) * sizeof(uint32_t)));
   t->view.overflow = t->view.items + kMaxFills + 1;
-  t->view.mask = static_cast<uint32_t>(t->capacity - 1);
+  t->view.cap = static_cast<uint32_t>(t->capacity);
   t->view.n2o_cap = static_cast<uint32_t>(max_items);
   XG_CUDA(cudaMemset(t->view.slots, 0xFF, t->capacity * sizeof(uint2)));
   XG_CUDA(cudaMemset(t->view.items, 0, (kMaxFills + 2) * sizeof(uint32_t)));

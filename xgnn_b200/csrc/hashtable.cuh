@@ -4,7 +4,10 @@
 // (reference: samgraph/common/cuda/cuda_hashtable.h:35-101, cuda_hashtable.cu:36-135).
 //
 // Layout in HBM (all per table, sized once for the worst-case batch):
-//   slots : uint2 {key, val}[capacity]   capacity = pow2 >= 2 * max_items, 0xFFFFFFFF'FFFFFFFF = free
+//   slots : uint2 {key, val}[capacity]   capacity = 1.25 x max_items by default (XG_TABLE_SLOTS_PCT): the
+//                                        worst-case batch of the headline config (8.45 M ids) gives an
+//                                        84 MB table that stays inside B200's 126 MB L2 while a batch
+//                                        is being sampled; 0xFFFFFFFF'FFFFFFFF = free
 //   n2o   : uint32[max_items]            local id -> global id  (the "unique" list, append only)
 //   items : uint32[kMaxFills + 1]        items[k] = number of unique ids after the k-th fill since
 //                                        Reset (items[0] = 0); lives on the device so that a whole
@@ -29,7 +32,7 @@ struct TableView {
   uint32_t *n2o_slot;  // [max_items] slot position of every numbered key: lets Reset clear only those
   uint32_t *items;     // [kMaxFills + 1]
   uint32_t *overflow;  // set to 1 if capacity was exceeded
-  uint32_t mask;       // capacity - 1
+  uint32_t cap;        // number of slots (any value, multiple of 2; not a power of two: sized to sit in L2)
   uint32_t n2o_cap;
 };
 
@@ -43,8 +46,8 @@ __device__ __forceinline__ uint32_t table_hash(uint32_t k) {
 // Claim (or find) the slot of `key`; fold `tagged_pos` into its val with atomicMin.
 // Returns the slot position, or kEmpty if the table is full.
 __device__ __forceinline__ uint32_t table_insert(const TableView &t, uint32_t key, uint32_t tagged_pos) {
-  uint32_t p = table_hash(key) & t.mask;
-  for (uint32_t probes = 0; probes <= t.mask; ++probes) {
+  uint32_t p = __umulhi(table_hash(key), t.cap);  // multiply-shift: any capacity, uses the hash's high bits
+  for (uint32_t probes = 0; probes < t.cap; ++probes) {
     uint32_t *kp = &t.slots[p].x;
     uint32_t k = *reinterpret_cast<volatile uint32_t *>(kp);
     if (k == kEmpty) k = atomicCAS(kp, kEmpty, key);
@@ -52,7 +55,7 @@ __device__ __forceinline__ uint32_t table_insert(const TableView &t, uint32_t ke
       atomicMin(&t.slots[p].y, tagged_pos);
       return p;
     }
-    p = (p + 1) & t.mask;
+    p = (p + 1 == t.cap) ? 0u : p + 1;
   }
   *t.overflow = 1;
   return kEmpty;
@@ -60,12 +63,12 @@ __device__ __forceinline__ uint32_t table_insert(const TableView &t, uint32_t ke
 
 // SearchO2N: slot position of `key`, kEmpty when absent.
 __device__ __forceinline__ uint32_t table_find(const TableView &t, uint32_t key) {
-  uint32_t p = table_hash(key) & t.mask;
-  for (uint32_t probes = 0; probes <= t.mask; ++probes) {
+  uint32_t p = __umulhi(table_hash(key), t.cap);
+  for (uint32_t probes = 0; probes < t.cap; ++probes) {
     uint32_t k = __ldg(&t.slots[p].x);
     if (k == key) return p;
     if (k == kEmpty) return kEmpty;
-    p = (p + 1) & t.mask;
+    p = (p + 1 == t.cap) ? 0u : p + 1;
   }
   return kEmpty;
 }

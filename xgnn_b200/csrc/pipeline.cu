@@ -403,7 +403,7 @@ int xg_sampler_submit(xg_sampler *s, const uint32_t *seeds, size_t num_seeds, in
     return XG_ERR_CUDA;
   }
   if (s->dirty.exchange(false)) {  // after an overflow the targeted Reset cannot know every used slot
-    const size_t cap = (size_t)s->view.mask + 1;
+    const size_t cap = (size_t)s->view.cap;
     if (cudaMemsetAsync(s->view.slots, 0xFF, cap * sizeof(uint2), st) != cudaSuccess ||
         cudaMemsetAsync(s->view.items, 0, (kMaxFills + 2) * sizeof(uint32_t), st) != cudaSuccess) {
       b->claimed.store(0);
