@@ -277,6 +277,19 @@ int xg_ipc_import(const unsigned char handle[64], void **out);
 int xg_ipc_close(void *p);
 int xg_enable_peer_access(int device, int peer);
 
+/* PartitionSolver::solve, cuda/dist_graph.cu:728-777 (search: :40-222; standalone twin
+ * utility/nvlink_placement_solver/solver.cc).  bandwidth = num_gpu x num_gpu row-major GB/s, 0 = no P2P
+ * path (the diagonal is the local bandwidth).  Outputs, all num_gpu x num_gpu row-major ints except
+ * out_num_parts[num_gpu]:  out_part_ids[g][0..out_num_parts[g]) = parts GPU g stores (ascending, rest -1)
+ * = GroupConfig::part_ids;  out_access[g][p] = GPU that g reads part p from = GroupConfig::ctx_group
+ * (cuda/dist_graph.h:217-229).  Same search order and tie-breaks as the reference, hence the same
+ * placement; on an all-to-all matrix (NVSwitch) the result is the identity placement. */
+int xg_partition_solve(const double *bandwidth, int num_gpu, int *out_num_parts, int *out_part_ids,
+                       int *out_access);
+/* PartitionSolver::DetectTopo_child, cuda/dist_graph.cu:779-884: out_bandwidth[d][p] = GB/s of a timed
+ * 128 MiB copy p -> d (0 when the pair has no P2P path); needs the GPUs. */
+int xg_detect_topology(int num_gpu, double *out_bandwidth);
+
 /* ------------------------------------------------------------------------------------------------
  * Synthetic datasets of the BASELINE.json shapes, generated in HBM (stand-in for datagen/ and
  * utility/data-process/, which need the network). Pure functions of (node, slot, seed); a shard is
