@@ -143,6 +143,34 @@ int xg_sample_khop(const xg_graph *g, int sample_type, const uint32_t *d_input, 
                    size_t fanout, uint32_t *d_out_src, uint32_t *d_out_dst, size_t *d_num_out,
                    uint64_t seed, uint64_t batch_key, void *stream);
 
+/* GPUSampleKHop1, cuda_sampling_khop1.cu:130-236: `fanout` draws with replacement per node; output grouped
+ * by ascending GLOBAL src id (stable), adjacent equal (src,dst) pairs collapsed. */
+int xg_sample_khop1(const xg_graph *g, const uint32_t *d_input, size_t num_input, size_t fanout,
+                    uint32_t *d_out_src, uint32_t *d_out_dst, size_t *d_num_out, uint64_t seed, uint64_t batch_key,
+                    void *stream);
+/* GPUSampleWeightedKHop (cuda_sampling_weighted_khop.cu:132-), ...Prefix (cuda_sampling_weighted_khop_prefix.cu
+ * :148-), ...HashDedup (cuda_sampling_weighted_khop_hash_dedup.cu:203-), selected by sample_type
+ * (XG_WEIGHTED_KHOP / _PREFIX / _HASH_DEDUP).  Tables are aligned with the flat CSR's indices
+ * (prob_table.bin f32, alias_table.bin u32 node ids, prob_prefix_table.bin f32); pass NULL for the ones the
+ * variant does not use.  The graph must be flat (num_part == 0), as in the reference. */
+int xg_sample_weighted_khop(const xg_graph *g, int sample_type, const float *d_prob_table,
+                            const uint32_t *d_alias_table, const float *d_prob_prefix_table, const uint32_t *d_input,
+                            size_t num_input, size_t fanout, uint32_t *d_out_src, uint32_t *d_out_dst,
+                            size_t *d_num_out, uint64_t seed, uint64_t batch_key, void *stream);
+/* GPUSampleRandomWalk<GraphType> + FrequencyHashmap::GetTopK, cuda_sampling_random_walk.cu:116-165,
+ * cuda_frequency_hashmap.cu:643-841.  Out arrays need num_input * K entries; d_out_data = visit counts. */
+int xg_sample_random_walk(const xg_graph *g, const uint32_t *d_input, size_t num_input, size_t random_walk_length,
+                          double random_walk_restart_prob, size_t num_random_walk, size_t K, uint32_t *d_out_src,
+                          uint32_t *d_out_dst, uint32_t *d_out_data, size_t *d_num_out, uint64_t seed,
+                          uint64_t batch_key, void *stream);
+/* Host-only test hooks: the four 32-bit words the kernels draw for Philox counter (c0,c1,c2,c3) under
+ * (seed, batch_key), and the third counter word the standalone samplers use.  Counters: KHop1 / weighted
+ * (input position, slot, salt, 0); hash-dedup (input position, try, salt, 1); random walk (input position,
+ * walk, step, salt). */
+void xg_philox4x32(uint64_t seed, uint64_t batch_key, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                   uint32_t out[4]);
+uint32_t xg_sample_salt(void);
+
 /* ------------------------------------------------------------------------------------------------
  * Extraction.
  */

@@ -355,3 +355,168 @@ size_t orc_minibatch(const uint32_t *indptr, const uint32_t *indices, const uint
   orc_table_destroy(t);
   return num_input;
 }
+
+/* ========================================================================================== */
+/* With-replacement / weighted samplers and random walk.  The reference has NO CPU twin for these
+ * (cpu/cpu_sampling_khop1.cc:24-27, cpu_sampling_weighted_khop.cc:24-28, cpu_sampling_random_walk.cc
+ * :24-28 are empty stubs), so these functions restate the CUDA files statement by statement, executed
+ * sequentially in thread-index order.  Random numbers are an INPUT (`rnd`, four 32-bit words per draw
+ * slot) so that a test can feed the very words the kernel under test consumed and compare bit for bit;
+ * how a word becomes a choice follows the reference (`curand() % len`, `curand_uniform() < prob`).
+ * "parity unpinned by the reference's tests": nothing in the reference pins these outputs. */
+
+static float orc_uniform_open0(uint32_t r) { return (float)((r >> 8) + 1u) * (1.0f / 16777216.0f); }
+static double orc_uniform_double(uint32_t r) { return ((double)r + 0.5) * (1.0 / 4294967296.0); }
+
+typedef struct { uint32_t src, dst; size_t idx; } orc_pair;
+static int orc_pair_cmp(const void *a, const void *b) {
+  const orc_pair *x = (const orc_pair *)a, *y = (const orc_pair *)b;
+  if (x->src != y->src) return x->src < y->src ? -1 : 1;
+  return x->idx < y->idx ? -1 : (x->idx > y->idx);   /* stable: cub::DeviceRadixSort::SortPairs on src only */
+}
+
+/* sort by src (stable) + keep the LAST of every run of equal (src,dst), drop padding:
+ * cuda/cuda_sampling_khop1.cu:74-128,170-224 (identical in the weighted variants) */
+static size_t orc_sort_dedup_adjacent(uint32_t *tmp_src, uint32_t *tmp_dst, size_t num, uint32_t *out_src,
+                                      uint32_t *out_dst) {
+  orc_pair *p = (orc_pair *)malloc((num + 1) * sizeof(orc_pair));
+  for (size_t t = 0; t < num; ++t) { p[t].src = tmp_src[t]; p[t].dst = tmp_dst[t]; p[t].idx = t; }
+  qsort(p, num, sizeof(orc_pair), orc_pair_cmp);
+  size_t w = 0;
+  for (size_t t = 0; t < num; ++t) {
+    int keep;
+    if (t + 1 < num) keep = (p[t].src != p[t + 1].src || p[t].dst != p[t + 1].dst) && p[t].src != ORC_EMPTY;
+    else keep = p[t].src != ORC_EMPTY;
+    if (keep) { out_src[w] = p[t].src; out_dst[w] = p[t].dst; ++w; }
+  }
+  free(p);
+  return w;
+}
+
+/* mode 1 = KHop1 (cuda_sampling_khop1.cu:42-72), 2 = alias (cuda_sampling_weighted_khop.cu:41-76),
+ * 4 = prefix (cuda_sampling_weighted_khop_prefix.cu:41-92).  rnd[(i*fanout+s)*4 + {0,1}] */
+size_t orc_sample_with_replacement(int mode, const uint32_t *indptr, const uint32_t *indices, const float *prob,
+                                   const uint32_t *alias, const float *prefix, const uint32_t *input,
+                                   size_t num_input, size_t fanout, const uint32_t *rnd, uint32_t *out_src,
+                                   uint32_t *out_dst) {
+  size_t num = num_input * fanout;
+  uint32_t *ts = (uint32_t *)malloc((num + 1) * sizeof(uint32_t));
+  uint32_t *td = (uint32_t *)malloc((num + 1) * sizeof(uint32_t));
+  for (size_t t = 0; t < num; ++t) {
+    const uint32_t rid = input[t / fanout];
+    const uint32_t off = indptr[rid], len = indptr[rid + 1] - indptr[rid];
+    const uint32_t r0 = rnd[t * 4 + 0], r1 = rnd[t * 4 + 1];
+    ts[t] = ORC_EMPTY; td[t] = ORC_EMPTY;
+    if (len == 0) continue;
+    ts[t] = rid;
+    if (mode == 1) {
+      td[t] = indices[off + r0 % len];
+    } else if (mode == 2) {
+      size_t k = r0 % len;
+      float r = orc_uniform_open0(r1);
+      td[t] = (r < prob[off + k]) ? indices[off + k] : alias[off + k];
+    } else {
+      const float up = prefix[off + len - 1];
+      float x = orc_uniform_open0(r0) * up;
+      if (x <= prefix[off]) td[t] = indices[off];
+      else {
+        size_t lo = off, hi = off + len - 1;
+        while (hi - lo >= 2) {
+          size_t mid = (lo + hi) >> 1;
+          if (prefix[mid] >= x) hi = mid; else lo = mid;
+        }
+        td[t] = indices[hi];
+      }
+    }
+  }
+  size_t n = orc_sort_dedup_adjacent(ts, td, num, out_src, out_dst);
+  free(ts); free(td);
+  return n;
+}
+
+/* cuda_sampling_weighted_khop_hash_dedup.cu:59-116 (+ count/compact :118-200): node-major, no sort.
+ * rnd[(i*budget + try)*4 + {0,1}], budget = tries_per_slot * fanout draws at most (the reference has no
+ * bound and spins forever when a node has fewer than `fanout` distinct outcomes). */
+size_t orc_sample_weighted_hash_dedup(const uint32_t *indptr, const uint32_t *indices, const float *prob,
+                                      const uint32_t *alias, const uint32_t *input, size_t num_input,
+                                      size_t fanout, size_t tries_per_slot, const uint32_t *rnd,
+                                      uint32_t *out_src, uint32_t *out_dst) {
+  size_t w = 0, budget = tries_per_slot * fanout;
+  uint32_t *seen = (uint32_t *)malloc((fanout + 1) * sizeof(uint32_t));
+  for (size_t i = 0; i < num_input; ++i) {
+    const uint32_t rid = input[i];
+    const uint32_t off = indptr[rid], len = indptr[rid + 1] - indptr[rid];
+    if (len <= fanout) {
+      for (size_t j = 0; j < len; ++j) { out_src[w] = rid; out_dst[w] = indices[off + j]; ++w; }
+      continue;
+    }
+    size_t have = 0;
+    for (size_t tries = 0; have < fanout && tries < budget; ++tries) {
+      const uint32_t r0 = rnd[(i * budget + tries) * 4 + 0], r1 = rnd[(i * budget + tries) * 4 + 1];
+      size_t k = r0 % len;
+      float r = orc_uniform_open0(r1);
+      uint32_t res = indices[off + k];
+      if (r > prob[off + k]) res = alias[off + k];
+      int dup = 0;
+      for (size_t q = 0; q < have; ++q) dup |= (seen[q] == res);
+      if (dup) continue;
+      seen[have++] = res;
+      out_src[w] = rid; out_dst[w] = res; ++w;
+    }
+  }
+  free(seen);
+  return w;
+}
+
+/* cuda_sampling_random_walk.cu:43-112 + FrequencyHashmap::GetTopK cuda_frequency_hashmap.cu:643-841.
+ * rnd[((i*num_walk + w)*walk_len + t)*4 + {0,1}].  Visit layout per seed: pos = t*num_walk + w (:66-80).
+ * Unique (seed, node) entries are listed in ascending order of the visit that created them (the bucket's
+ * `index`; sequential execution => the first visit), then sorted stably, descending, on the 64-bit key
+ * ((N - i) << 32 | count) (:737-746) and the first min(K, #unique) per seed are emitted (:500-532). */
+typedef struct { uint64_t key; uint32_t dst; size_t ord; } orc_freq;
+static int orc_freq_cmp(const void *a, const void *b) {
+  const orc_freq *x = (const orc_freq *)a, *y = (const orc_freq *)b;
+  if (x->key != y->key) return x->key > y->key ? -1 : 1;
+  return x->ord < y->ord ? -1 : (x->ord > y->ord);
+}
+size_t orc_random_walk_topk(const uint32_t *indptr, const uint32_t *indices, const uint32_t *input,
+                            size_t num_input, size_t walk_len, double restart_prob, size_t num_walk, size_t K,
+                            const uint32_t *rnd, uint32_t *out_src, uint32_t *out_dst, uint32_t *out_data) {
+  const size_t M = walk_len * num_walk;
+  uint32_t *vis = (uint32_t *)malloc((M + 1) * sizeof(uint32_t));
+  orc_freq *fr = (orc_freq *)malloc((M + 1) * sizeof(orc_freq));
+  size_t w_out = 0;
+  for (size_t i = 0; i < num_input; ++i) {
+    for (size_t w = 0; w < num_walk; ++w) {
+      uint32_t node = input[i];
+      for (size_t t = 0; t < walk_len; ++t) {
+        size_t pos = t * num_walk + w;
+        vis[pos] = ORC_EMPTY;
+        if (node == ORC_EMPTY) continue;
+        const uint32_t off = indptr[node], len = indptr[node + 1] - indptr[node];
+        if (len == 0) { node = ORC_EMPTY; continue; }
+        const uint32_t *r = rnd + ((i * num_walk + w) * walk_len + t) * 4;
+        size_t k = r[0] % len;
+        vis[pos] = indices[off + k];
+        node = indices[off + k];
+        if (orc_uniform_double(r[1]) < restart_prob) node = ORC_EMPTY;
+      }
+    }
+    size_t nu = 0;
+    for (size_t m = 0; m < M; ++m) {
+      if (vis[m] == ORC_EMPTY) continue;
+      size_t q = 0;
+      for (; q < nu; ++q) if (fr[q].dst == vis[m]) break;
+      if (q == nu) { fr[nu].dst = vis[m]; fr[nu].key = 0; fr[nu].ord = nu; ++nu; }
+      fr[q].key += 1;
+    }
+    for (size_t q = 0; q < nu; ++q) fr[q].key |= ((uint64_t)(num_input - i)) << 32;
+    qsort(fr, nu, sizeof(orc_freq), orc_freq_cmp);
+    size_t take = nu < K ? nu : K;
+    for (size_t q = 0; q < take; ++q) {
+      out_src[w_out] = input[i]; out_dst[w_out] = fr[q].dst; out_data[w_out] = (uint32_t)fr[q].key; ++w_out;
+    }
+  }
+  free(vis); free(fr);
+  return w_out;
+}

@@ -46,6 +46,13 @@ _sig(orc, "orc_miss_cache_index", None, u32p, u32p, c_size_t, u32p, u32p, POINTE
      POINTER(c_size_t))
 _sig(orc, "orc_partition_features", c_size_t, c_void_p, c_size_t, u32p, c_size_t, c_uint32, c_uint32, c_void_p)
 _sig(orc, "orc_extract_ggms", None, c_void_p, c_size_t, u32p, c_size_t, c_void_p, c_void_p, c_void_p, c_uint32)
+f32p = np.ctypeslib.ndpointer(dtype=np.float32, flags="C_CONTIGUOUS")
+_sig(orc, "orc_sample_with_replacement", c_size_t, c_int, u32p, u32p, c_void_p, c_void_p, c_void_p, u32p, c_size_t,
+     c_size_t, u32p, u32p, u32p)
+_sig(orc, "orc_sample_weighted_hash_dedup", c_size_t, u32p, u32p, f32p, u32p, u32p, c_size_t, c_size_t, c_size_t, u32p,
+     u32p, u32p)
+_sig(orc, "orc_random_walk_topk", c_size_t, u32p, u32p, u32p, c_size_t, c_size_t, c_double, c_size_t, c_size_t, u32p,
+     u32p, u32p, u32p)
 
 
 def u32(a) -> np.ndarray:
@@ -59,6 +66,40 @@ def sample_khop0(indptr, indices, inp, fanout, seed=1):
     dst = np.empty(max(len(inp) * fanout, 1), np.uint32)
     n = orc.orc_sample_khop0(u32(indptr), u32(indices), inp, len(inp), fanout, src, dst, seed)
     return src[:n].copy(), dst[:n].copy()
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data
+
+
+def sample_with_replacement(mode, indptr, indices, inp, fanout, rnd, prob=None, alias=None, prefix=None):
+    """mode 1 = KHop1, 2 = alias, 4 = prefix (SampleType numbering); rnd = uint32 [n * fanout, 4]"""
+    inp = u32(inp)
+    n = max(len(inp) * fanout, 1)
+    src, dst = np.empty(n, np.uint32), np.empty(n, np.uint32)
+    keep = [np.ascontiguousarray(x) if x is not None else None for x in (prob, alias, prefix)]
+    m = orc.orc_sample_with_replacement(mode, u32(indptr), u32(indices), _p(keep[0]), _p(keep[1]), _p(keep[2]), inp,
+                                        len(inp), fanout, np.ascontiguousarray(rnd).reshape(-1), src, dst)
+    return src[:m].copy(), dst[:m].copy()
+
+
+def sample_weighted_hash_dedup(indptr, indices, inp, fanout, rnd, prob, alias, tries_per_slot=16):
+    inp = u32(inp)
+    n = max(len(inp) * fanout, 1)
+    src, dst = np.empty(n, np.uint32), np.empty(n, np.uint32)
+    m = orc.orc_sample_weighted_hash_dedup(u32(indptr), u32(indices), np.ascontiguousarray(prob, np.float32),
+                                           u32(alias), inp, len(inp), fanout, tries_per_slot,
+                                           np.ascontiguousarray(rnd).reshape(-1), src, dst)
+    return src[:m].copy(), dst[:m].copy()
+
+
+def random_walk_topk(indptr, indices, inp, walk_len, restart_prob, num_walk, K, rnd):
+    inp = u32(inp)
+    n = max(len(inp) * K, 1)
+    outs = [np.empty(n, np.uint32) for _ in range(3)]
+    m = orc.orc_random_walk_topk(u32(indptr), u32(indices), inp, len(inp), walk_len, restart_prob, num_walk, K,
+                                 np.ascontiguousarray(rnd).reshape(-1), *outs)
+    return tuple(o[:m].copy() for o in outs)
 
 
 class Table:

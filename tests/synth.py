@@ -63,3 +63,44 @@ def degree_rank(indptr):
     """nodes by out-degree, descending, stable (utility/data-process/toolkit/cache/cache_by_degree.cc:29-63)"""
     deg = np.diff(indptr.astype(np.int64))
     return np.argsort(-deg, kind="stable").astype(np.uint32)
+
+
+def edge_weights(indptr, indices, seed=11):
+    """positive per-edge weights (seeded); a few zero-probability edges exercise the alias fallback"""
+    rng = np.random.default_rng(seed)
+    w = rng.random(int(indptr[-1])).astype(np.float64) + 0.05
+    w[rng.random(len(w)) < 0.05] *= 20.0
+    return w
+
+
+def alias_tables(indptr, indices, weights):
+    """Vose alias tables per node, laid out like prob_table.bin / alias_table.bin
+    (utility/data-process/toolkit/weight/create_alias_table.cc): prob f32[E], alias u32[E] holding NODE IDS."""
+    E = int(indptr[-1])
+    prob = np.ones(E, np.float32)
+    alias = indices.copy().astype(np.uint32)
+    for v in range(len(indptr) - 1):
+        b, e = int(indptr[v]), int(indptr[v + 1])
+        n = e - b
+        if n == 0:
+            continue
+        p = weights[b:e] / weights[b:e].sum() * n
+        small = [i for i in range(n) if p[i] < 1.0]
+        large = [i for i in range(n) if p[i] >= 1.0]
+        while small and large:
+            s, l = small.pop(), large.pop()
+            prob[b + s] = p[s]
+            alias[b + s] = indices[b + l]
+            p[l] = p[l] + p[s] - 1.0
+            (small if p[l] < 1.0 else large).append(l)
+    return prob, alias
+
+
+def prefix_table(indptr, weights):
+    """per-node running sums of normalised weights (create_prob_prefix_table.cc:94-131), f32[E]"""
+    out = np.zeros(int(indptr[-1]), np.float32)
+    for v in range(len(indptr) - 1):
+        b, e = int(indptr[v]), int(indptr[v + 1])
+        if e > b:
+            out[b:e] = np.cumsum(weights[b:e] / weights[b:e].sum()).astype(np.float32)
+    return out

@@ -121,6 +121,15 @@ _sig("xg_map_edges", c_int, c_void_p, _u32p, _u32p, _u32p, _u32p, c_size_t, c_vo
 _sig("xg_sample_khop", c_int, POINTER(XgGraph), c_int, _u32p, c_size_t, c_size_t, _u32p, _u32p, c_void_p,
      c_uint64, c_uint64, c_void_p)
 
+_sig("xg_sample_khop1", c_int, POINTER(XgGraph), _u32p, c_size_t, c_size_t, _u32p, _u32p, c_void_p, c_uint64, c_uint64,
+     c_void_p)
+_sig("xg_sample_weighted_khop", c_int, POINTER(XgGraph), c_int, c_void_p, c_void_p, c_void_p, _u32p, c_size_t, c_size_t,
+     _u32p, _u32p, c_void_p, c_uint64, c_uint64, c_void_p)
+_sig("xg_sample_random_walk", c_int, POINTER(XgGraph), _u32p, c_size_t, c_size_t, c_double, c_size_t, c_size_t, _u32p,
+     _u32p, _u32p, c_void_p, c_uint64, c_uint64, c_void_p)
+_sig("xg_philox4x32", None, c_uint64, c_uint64, c_uint32, c_uint32, c_uint32, c_uint32, POINTER(c_uint32))
+_sig("xg_sample_salt", c_uint32)
+
 # ---- extraction -----------------------------------------------------------------------------
 _sig("xg_extract", c_int, c_void_p, c_void_p, _u32p, c_size_t, c_size_t, c_int, c_void_p)
 _sig("xg_extract_ggms", c_int, POINTER(XgFeatureStore), _u32p, c_size_t, c_void_p, c_void_p, c_void_p)

@@ -25,31 +25,6 @@ namespace xg {
 
 namespace {
 
-struct NodeRoute {
-  const uint32_t *indptr;
-  const uint32_t *indices;
-  uint32_t row;
-};
-
-__device__ __forceinline__ NodeRoute route(const xg_graph &g, uint32_t v) {
-  NodeRoute r;
-  if (g.num_part == 0) {
-    r.indptr = g.part_indptr[0];
-    r.indices = g.part_indices[0];
-    r.row = v;
-  } else if (v < g.num_cache_node) {
-    const uint32_t part = v % g.num_part;
-    r.indptr = g.part_indptr[part];
-    r.indices = g.part_indices[part];
-    r.row = v / g.num_part;
-  } else {  // host-resident tail of the graph: slot [num_part] holds the whole CSR
-    r.indptr = g.part_indptr[g.num_part];
-    r.indices = g.part_indices[g.num_part];
-    r.row = v;
-  }
-  return r;
-}
-
 template <int G, int VPL, bool FUSED>
 __global__ void __launch_bounds__(kSampleBlock)
 sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint32_t num_input_max,

@@ -151,6 +151,46 @@ def GPUSampleKHop(graph: XgGraph, input: torch.Tensor, fanout: int, *, seed: int
     return out_src[:e], out_dst[:e]
 
 
+def GPUSampleKHop1(graph: XgGraph, input: torch.Tensor, fanout: int, *, seed: int = 0, batch_key: int = 0):
+    """GPUSampleKHop1 (cuda/cuda_sampling_khop1.cu:130-236) -> (out_src, out_dst), trimmed."""
+    n = input.numel()
+    out_src = torch.empty(max(n * fanout, 1), dtype=torch.int32, device=input.device)
+    out_dst = torch.empty(max(n * fanout, 1), dtype=torch.int32, device=input.device)
+    num_out = torch.zeros(1, dtype=torch.int64, device=input.device)
+    check(lib.xg_sample_khop1(byref(graph), _ptr(_ids(input)), n, fanout, _ptr(out_src), _ptr(out_dst), _ptr(num_out),
+                              seed, batch_key, _stream()))
+    e = int(num_out.item())
+    return out_src[:e], out_dst[:e]
+
+
+def GPUSampleWeightedKHop(graph: XgGraph, input: torch.Tensor, fanout: int, *, prob_table=None, alias_table=None,
+                          prob_prefix_table=None, sample_type: int = kWeightedKHop, seed: int = 0, batch_key: int = 0):
+    """GPUSampleWeightedKHop / ...Prefix / ...HashDedup (cuda/cuda_sampling_weighted_khop*.cu)."""
+    n = input.numel()
+    out_src = torch.empty(max(n * fanout, 1), dtype=torch.int32, device=input.device)
+    out_dst = torch.empty(max(n * fanout, 1), dtype=torch.int32, device=input.device)
+    num_out = torch.zeros(1, dtype=torch.int64, device=input.device)
+    check(lib.xg_sample_weighted_khop(byref(graph), sample_type, _ptr(prob_table), _ptr(alias_table),
+                                      _ptr(prob_prefix_table), _ptr(_ids(input)), n, fanout, _ptr(out_src),
+                                      _ptr(out_dst), _ptr(num_out), seed, batch_key, _stream()))
+    e = int(num_out.item())
+    return out_src[:e], out_dst[:e]
+
+
+def GPUSampleRandomWalk(graph: XgGraph, input: torch.Tensor, random_walk_length: int, random_walk_restart_prob: float,
+                        num_random_walk: int, K: int, *, seed: int = 0, batch_key: int = 0):
+    """GPUSampleRandomWalk + FrequencyHashmap::GetTopK (cuda/cuda_sampling_random_walk.cu:116-165)
+    -> (out_src, out_dst, out_data = visit counts), trimmed."""
+    n = input.numel()
+    outs = [torch.empty(max(n * K, 1), dtype=torch.int32, device=input.device) for _ in range(3)]
+    num_out = torch.zeros(1, dtype=torch.int64, device=input.device)
+    check(lib.xg_sample_random_walk(byref(graph), _ptr(_ids(input)), n, random_walk_length, random_walk_restart_prob,
+                                    num_random_walk, K, _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2]), _ptr(num_out),
+                                    seed, batch_key, _stream()))
+    e = int(num_out.item())
+    return outs[0][:e], outs[1][:e], outs[2][:e]
+
+
 def GPUExtract(src: torch.Tensor | int, index: torch.Tensor, dim: int | None = None,
                dtype: torch.dtype | None = None) -> torch.Tensor:
     """cuda::GPUExtract (cuda/cuda_extraction.cu:74-116). `src` is a [num_node, dim] tensor on the device or in
