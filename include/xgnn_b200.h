@@ -226,7 +226,7 @@ typedef struct xg_sampler_config {
   uint32_t num_layer;
   uint32_t fanout[XG_MAX_LAYERS]; /* indexed by layer; consumed last -> first (dist_loops.cc:120-123) */
   uint32_t batch_size;            /* most seeds one minibatch can carry */
-  int32_t sample_type;            /* XG_KHOP0 / XG_KHOP2 / XG_KHOP3 */
+  int32_t sample_type;            /* any SampleType; KHop0/2/3 run the fused sample+insert kernel */
   uint32_t num_slots;             /* minibatches that may be alive at once; 0 -> 2 */
   uint32_t flags;
   uint32_t feat_dim;
@@ -235,6 +235,14 @@ typedef struct xg_sampler_config {
   uint64_t max_input_nodes;       /* 0 -> PredictNumNodes(batch_size, fanout) (common.cc:488-497),
                                      clipped to the number of nodes */
   void *stream;                   /* cudaStream_t all work is enqueued on; NULL -> a private stream */
+  /* sample_type == XG_RANDOM_WALK (operation.cc:163-175): fanout[l] = num_neighbor (K) for every layer */
+  uint32_t random_walk_length;
+  uint32_t num_random_walk;
+  double random_walk_restart_prob;
+  /* weighted samplers: tables aligned with the flat CSR (NULL otherwise) */
+  const float *prob_table;
+  const uint32_t *alias_table;
+  const float *prob_prefix_table;
 } xg_sampler_config;
 
 /* One finished Task (common.h:246-285). Pointers are device pointers owned by the batch; they stay

@@ -145,3 +145,78 @@ def test_slots_exhausted_is_reported(ops, small):
     a.release()
     sm.sample(seeds)
     del b
+
+
+# ---- the engine with the non-uniform samplers: replay the Philox words through the oracle, layer by layer ----
+def oracle_minibatch_ext(g, seeds, fan, sample_type, seed, batch_key, rw=None):
+    import philox
+    L = len(fan)
+    table = O.Table(200000)
+    table.populate(seeds)
+    cur = seeds.copy()
+    out = {"row": [None] * L, "col": [None] * L, "data": [None] * L, "num_src": [0] * L, "num_dst": [0] * L}
+    for l in range(L - 1, -1, -1):
+        salt = philox.SALT + l
+        n = len(cur)
+        if sample_type == 3:
+            Lw, p, W = rw
+            src, dst, cnt = O.random_walk_topk(g["indptr"], g["indices"], cur, Lw, p, W, fan[l],
+                                               philox.words_walks(seed, batch_key, n, W, Lw, salt=salt))
+            out["data"][l] = cnt
+        elif sample_type == 6:
+            src, dst = O.sample_weighted_hash_dedup(g["indptr"], g["indices"], cur, fan[l],
+                                                    philox.words_slots(seed, batch_key, n, 16 * fan[l], c3=1, salt=salt),
+                                                    g["prob"], g["alias"])
+        else:
+            src, dst = O.sample_with_replacement(sample_type, g["indptr"], g["indices"], cur, fan[l],
+                                                 philox.words_slots(seed, batch_key, n, fan[l], salt=salt),
+                                                 prob=g["prob"], alias=g["alias"], prefix=g["prefix"])
+        table.populate(dst)
+        out["col"][l], out["row"][l] = table.map_edges(src, dst)
+        out["num_dst"][l], out["num_src"][l] = n, table.num_items()
+        cur = table.unique()
+    out["input_nodes"] = cur
+    return out
+
+
+@pytest.fixture(scope="module")
+def wgraph():
+    V, E = 4000, 36000
+    indptr, indices = synth.make_graph(V, E, seed=33, max_deg=40)
+    w = synth.edge_weights(indptr, indices)
+    prob, alias = synth.alias_tables(indptr, indices, w)
+    return dict(V=V, indptr=indptr, indices=indices, prob=prob, alias=alias, prefix=synth.prefix_table(indptr, w),
+                feat=synth.make_features(V, 16), label=synth.make_labels(V))
+
+
+@pytest.mark.parametrize("use_graph", [True, False])
+@pytest.mark.parametrize("sample_type", [1, 2, 4, 6, 3])
+def test_minibatch_other_samplers_bit_exact_vs_oracle_replay(ops, wgraph, sample_type, use_graph):
+    g = ops.make_graph(dev(wgraph["indptr"]), dev(wgraph["indices"]))
+    store = ops.make_feature_store(16 * 4, dev(wgraph["feat"]))
+    fan, B = ([5, 5] if sample_type == 3 else [4, 6]), 200
+    kw = {}
+    if sample_type in (2, 6):
+        kw = dict(prob_table=dev(wgraph["prob"]), alias_table=dev(wgraph["alias"]))
+    if sample_type == 4:
+        kw = dict(prob_prefix_table=dev(wgraph["prefix"]))
+    if sample_type == 3:
+        kw = dict(random_walk_length=3, num_random_walk=4, random_walk_restart_prob=0.5)
+    sm = ops.MinibatchSampler(g, fan, B, store=store, feat_dim=16, label=dev(wgraph["label"]), seed=77,
+                              sample_type=sample_type, use_graph=use_graph, **kw)
+    train = synth.train_set(wgraph["V"], 0.3)
+    for step in range(3):
+        seeds = train[step * B:(step + 1) * B].copy()
+        if step == 1:
+            seeds[3] = seeds[0]  # arch6 seeds may hold wrapped-around duplicates
+        mb = sm.sample(seeds, batch_key=step)
+        ref = oracle_minibatch_ext(wgraph, seeds, fan, sample_type, 77, step, rw=(3, 0.5, 4))
+        assert np.array_equal(u32(mb.input_nodes), ref["input_nodes"])
+        for l in range(len(fan)):
+            assert np.array_equal(u32(mb.col(l)), ref["col"][l]) and np.array_equal(u32(mb.row(l)), ref["row"][l])
+            assert mb.num_src[l] == ref["num_src"][l] and mb.num_dst[l] == ref["num_dst"][l]
+            if sample_type == 3:
+                assert np.array_equal(u32(mb.data(l)), ref["data"][l])
+        assert mb.feat.cpu().numpy().tobytes() == wgraph["feat"][ref["input_nodes"]].tobytes()
+        assert np.array_equal(mb.label.cpu().numpy(), wgraph["label"][seeds])
+        mb.release()

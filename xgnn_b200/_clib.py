@@ -55,6 +55,12 @@ class XgSamplerConfig(Structure):
         ("seed", c_uint64),
         ("max_input_nodes", c_uint64),
         ("stream", c_void_p),
+        ("random_walk_length", c_uint32),
+        ("num_random_walk", c_uint32),
+        ("random_walk_restart_prob", c_double),
+        ("prob_table", c_void_p),
+        ("alias_table", c_void_p),
+        ("prob_prefix_table", c_void_p),
     ]
 
 

@@ -11,6 +11,7 @@
 // All buffers are sized once for the worst-case batch (PredictNumNodes, common.cc:488-497) so the
 // chain has a fixed shape and is captured once per batch slot as a CUDA graph and replayed: one
 // launch call per minibatch, no host synchronisation until the consumer asks for the batch.
+#include <algorithm>
 #include <atomic>
 #include <cstdlib>
 #include <cstring>
@@ -74,7 +75,7 @@ struct xg_batch {
   std::atomic<int> claimed{0};
   // device
   uint32_t *seeds = nullptr, *seed_local = nullptr, *input_nodes = nullptr;
-  uint32_t *row[XG_MAX_LAYERS] = {}, *col[XG_MAX_LAYERS] = {};
+  uint32_t *row[XG_MAX_LAYERS] = {}, *col[XG_MAX_LAYERS] = {}, *data[XG_MAX_LAYERS] = {};
   void *feat = nullptr;
   int64_t *label = nullptr;
   BatchParams *d_params = nullptr;
@@ -112,6 +113,9 @@ struct xg_sampler {
   bool own_stream = false;
   bool use_graph = true;
   bool stage_timing = false;
+  bool uniform = true;      // KHop0/2/3: fused sample + insert kernel
+  ExtWorkspace ext;         // scratch of the with-replacement / weighted samplers
+  WeightTables weights;
   uint32_t launches_per_batch = 0;
   std::mutex mu;
   std::vector<xg_batch *> slots;
@@ -140,6 +144,7 @@ int alloc_slot(xg_sampler *s, xg_batch **out) {
   for (uint32_t l = 0; l < L; ++l) {
     XG_CUDA(cudaMalloc(&b->row[l], s->cap_edge[l] * sizeof(uint32_t)));
     XG_CUDA(cudaMalloc(&b->col[l], s->cap_edge[l] * sizeof(uint32_t)));
+    if (s->cfg.sample_type == XG_RANDOM_WALK) XG_CUDA(cudaMalloc(&b->data[l], s->cap_edge[l] * sizeof(uint32_t)));
   }
   if (s->has_store) XG_CUDA(cudaMalloc(&b->feat, s->cap_input * s->row_bytes));
   if (s->label) XG_CUDA(cudaMalloc(&b->label, B * sizeof(int64_t)));
@@ -169,6 +174,7 @@ void free_slot(xg_batch *b) {
   for (int l = 0; l < XG_MAX_LAYERS; ++l) {
     cudaFree(b->row[l]);
     cudaFree(b->col[l]);
+    cudaFree(b->data[l]);
   }
   cudaFree(b->feat);
   cudaFree(b->label);
@@ -208,17 +214,36 @@ int enqueue_batch(xg_sampler *s, xg_batch *b) {
     const int fill = (L - 1 - l) + 2;
     const bool seed_layer = (l == L - 1);
     XG_CUDA(cudaMemsetAsync(s->scan_mem, 0, s->scan_bytes, st));
-    SampleFusion fusion{};
-    fusion.table = t;
-    fusion.pos_out = s->pos;
-    fusion.src_local = seed_layer ? b->seed_local : nullptr;  // later inputs ARE the unique list: local id == position
-    fusion.enabled = true;
     uint64_t *d_num_edge = &b->d_counts->num_edge[l];
-    rc = launch_sample_uniform(s->graph, seed_layer ? b->seeds : t.n2o, s->cap_in[l],
-                               seed_layer ? d_nseed32 : &t.items[fill - 1], s->cfg.fanout[l], b->col[l],
-                               s->dst_global, d_num_edge, 0, 0, &b->d_params->rng_key,
-                               kSampleSalt + (uint32_t)l, fusion, scan_a(s), st);
-    if (rc) return rc;
+    const uint32_t *in_nodes = seed_layer ? b->seeds : t.n2o;
+    const uint32_t *d_num_in = seed_layer ? d_nseed32 : &t.items[fill - 1];
+    // later inputs ARE the unique list: local id == position
+    const uint32_t *src_local = seed_layer ? b->seed_local : nullptr;
+    const uint32_t salt = kSampleSalt + (uint32_t)l;
+    if (s->uniform) {
+      SampleFusion fusion{};
+      fusion.table = t;
+      fusion.pos_out = s->pos;
+      fusion.src_local = src_local;
+      fusion.enabled = true;
+      rc = launch_sample_uniform(s->graph, in_nodes, s->cap_in[l], d_num_in, s->cfg.fanout[l], b->col[l], s->dst_global,
+                                 d_num_edge, 0, 0, &b->d_params->rng_key, salt, fusion, scan_a(s), st);
+      if (rc) return rc;
+    } else {
+      if (s->cfg.sample_type == XG_RANDOM_WALK) {
+        rc = launch_random_walk(s->graph, in_nodes, s->cap_in[l], d_num_in, s->cfg.random_walk_length,
+                                s->cfg.random_walk_restart_prob, s->cfg.num_random_walk, s->cfg.fanout[l], true,
+                                src_local, b->col[l], s->dst_global, b->data[l], d_num_edge, make_uint2(0, 0),
+                                &b->d_params->rng_key, salt, scan_a(s), st);
+      } else {
+        rc = launch_sample_ext(s->cfg.sample_type, s->graph, s->weights, in_nodes, s->cap_in[l], d_num_in,
+                               s->cfg.fanout[l], true, src_local, b->col[l], s->dst_global, d_num_edge,
+                               make_uint2(0, 0), &b->d_params->rng_key, salt, s->ext, st);
+      }
+      if (rc) return rc;
+      // unfused: the neighbours go into the table in a pass of their own
+      if ((rc = launch_table_insert(t, s->dst_global, s->pos, s->cap_edge[l], d_num_edge, st))) return rc;
+    }
     mark();
     // FillWithDuplicates(out_dst) + GPUMapEdges (dist_loops.cc:279-297): number the new ids, then
     // one 8-byte load per edge at the remembered slot gives the neighbour's local id
@@ -278,8 +303,17 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
   XG_REQUIRE(out && graph && cfg, "NULL argument");
   XG_REQUIRE(cfg->num_layer >= 1 && cfg->num_layer <= XG_MAX_LAYERS, "num_layer must be in [1, 8]");
   XG_REQUIRE(cfg->batch_size >= 1, "batch_size is 0");
-  XG_REQUIRE(cfg->sample_type == XG_KHOP0 || cfg->sample_type == XG_KHOP2 || cfg->sample_type == XG_KHOP3,
-             "the fused minibatch engine runs the uniform samplers (KHop0 / KHop2 / KHop3)");
+  XG_REQUIRE(cfg->sample_type >= XG_KHOP0 && cfg->sample_type <= XG_KHOP3, "unknown sample_type");
+  const bool uniform = cfg->sample_type == XG_KHOP0 || cfg->sample_type == XG_KHOP2 || cfg->sample_type == XG_KHOP3;
+  if (cfg->sample_type == XG_RANDOM_WALK) {
+    XG_REQUIRE(cfg->random_walk_length >= 1 && cfg->num_random_walk >= 1, "random walk needs length and walks >= 1");
+    XG_REQUIRE((uint64_t)cfg->random_walk_length * cfg->num_random_walk <= 512, "walk_length * num_walk must be <= 512");
+  }
+  if (cfg->sample_type == XG_WEIGHTED_KHOP || cfg->sample_type == XG_WEIGHTED_KHOP_HASH_DEDUP)
+    XG_REQUIRE(cfg->prob_table && cfg->alias_table, "weighted KHop needs prob_table and alias_table");
+  if (cfg->sample_type == XG_WEIGHTED_KHOP_PREFIX) XG_REQUIRE(cfg->prob_prefix_table, "prob_prefix_table is NULL");
+  if (!uniform && cfg->sample_type != XG_KHOP1 && cfg->sample_type != XG_RANDOM_WALK)
+    XG_REQUIRE(graph->num_part == 0, "weighted samplers take the flat CSR their tables are aligned with");
   XG_REQUIRE(graph->num_part <= XG_MAX_PARTS, "too many partitions");
   DeviceScope scope(device);
   auto *s = new xg_sampler();
@@ -287,6 +321,10 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
   s->graph = *graph;
   s->cfg = *cfg;
   s->label = label;
+  s->uniform = uniform;
+  s->weights.prob = cfg->prob_table;
+  s->weights.alias = cfg->alias_table;
+  s->weights.prefix = cfg->prob_prefix_table;
   if (store) {
     s->store = *store;
     s->has_store = true;
@@ -321,7 +359,8 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
   size_t max_edge = cfg->batch_size, tiles_a = 1, tiles_b = (cfg->batch_size + kAssignTile - 1) / kAssignTile;
   for (int l = 0; l < L; ++l) {
     if (s->cap_edge[l] > max_edge) max_edge = s->cap_edge[l];
-    const size_t ta = (s->cap_in[l] + kSampleTile - 1) / kSampleTile;
+    // random walk scans over 64-seed tiles, the k-hop kernels over kSampleTile nodes
+    const size_t ta = (s->cap_in[l] + 63) / 64;
     const size_t tb = (s->cap_edge[l] + kAssignTile - 1) / kAssignTile;
     if (ta > tiles_a) tiles_a = ta;
     if (tb > tiles_b) tiles_b = tb;
@@ -339,6 +378,21 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
   XG_CUDA(cudaMalloc(&s->dst_global, max_edge * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&s->pos, max_edge * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&s->scan_mem, s->scan_bytes));
+  if (!uniform && cfg->sample_type != XG_RANDOM_WALK) {
+    size_t max_in = 1, max_f = 1;
+    for (int l = 0; l < L; ++l) {
+      if (s->cap_in[l] > max_in) max_in = s->cap_in[l];
+      if (cfg->fanout[l] > max_f) max_f = cfg->fanout[l];
+    }
+    // cap_slots must cover the largest layer: reserve by the largest product
+    size_t max_slots = 1;
+    for (int l = 0; l < L; ++l) max_slots = std::max(max_slots, s->cap_edge[l]);
+    if ((rc = ext_reserve(s->ext, max_in, (max_slots + max_in - 1) / max_in, nullptr))) {
+      xg_sampler_destroy(s);
+      return rc;
+    }
+    (void)max_f;
+  }
   if (cfg->stream) {
     s->stream = as_stream(cfg->stream);
   } else {
@@ -370,6 +424,7 @@ int xg_sampler_destroy(xg_sampler *s) {
   cudaFree(s->dst_global);
   cudaFree(s->pos);
   cudaFree(s->scan_mem);
+  ext_release(s->ext);
   if (s->table) xg_hashtable_destroy(s->table);
   if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
   delete s;
@@ -503,7 +558,7 @@ int xg_batch_wait(xg_batch *b, xg_batch_view *view) {
     const int fill = (L - 1 - l) + 2;
     view->row[l] = b->row[l];
     view->col[l] = b->col[l];
-    view->data[l] = nullptr;
+    view->data[l] = b->data[l];
     view->num_dst[l] = (l == L - 1) ? b->num_seeds : c.items[fill - 1];  // num_dst = num_input (dist_loops.cc:304-306)
     view->num_src[l] = c.items[fill];
     view->num_edge[l] = c.num_edge[l];

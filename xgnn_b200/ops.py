@@ -312,6 +312,10 @@ class Minibatch:
     def col(self, l):
         return self._t(self.view.col[l], (self.num_edge[l],), torch.int32)
 
+    def data(self, l):
+        """per-edge payload (random-walk visit counts), samgraph_torch_get_graph_data"""
+        return self._t(self.view.data[l], (self.num_edge[l],), torch.int32) if self.view.data[l] else None
+
     @property
     def input_nodes(self):
         return self._t(self.view.input_nodes, (self.num_input,), torch.int32)
@@ -346,7 +350,9 @@ class MinibatchSampler:
                  feat_dim: int = 0, feat_dtype: torch.dtype = torch.float32, label: torch.Tensor | int | None = None,
                  sample_type: int = kKHop0, seed: int = 0, num_slots: int = 2, max_input_nodes: int = 0,
                  device: int = 0, use_graph: bool = True, stream: torch.cuda.Stream | None = None,
-                 stage_timing: bool = False):
+                 stage_timing: bool = False, random_walk_length: int = 0, num_random_walk: int = 0,
+                 random_walk_restart_prob: float = 0.0, prob_table: torch.Tensor | None = None,
+                 alias_table: torch.Tensor | None = None, prob_prefix_table: torch.Tensor | None = None):
         cfg = _clib.XgSamplerConfig()
         cfg.num_layer = len(fanout)
         for i, f in enumerate(fanout):
@@ -360,9 +366,12 @@ class MinibatchSampler:
         cfg.seed = seed
         cfg.max_input_nodes = max_input_nodes
         cfg.stream = stream.cuda_stream if stream is not None else None
+        cfg.random_walk_length, cfg.num_random_walk = random_walk_length, num_random_walk
+        cfg.random_walk_restart_prob = random_walk_restart_prob
+        cfg.prob_table, cfg.alias_table, cfg.prob_prefix_table = _ptr(prob_table), _ptr(alias_table), _ptr(prob_prefix_table)
         self.device = torch.device("cuda", device)
         self.feat_dim, self.feat_dtype = feat_dim, feat_dtype
-        self._keep = [graph, store, label, stream]
+        self._keep = [graph, store, label, stream, prob_table, alias_table, prob_prefix_table]
         h = c_void_p()
         lp = label if isinstance(label, int) or label is None else label.data_ptr()
         check(lib.xg_sampler_create(byref(h), byref(graph), byref(store) if store is not None else None, lp,
