@@ -374,3 +374,745 @@ struct SharedBlock {
 };
 
 }  // namespace sam
+
+#include <cub/device/device_scan.cuh>
+
+namespace sam {
+
+// ---------------------------------------------------------------------------------------------------
+// One finished Task, shared between the pool, the "current batch" and every tensor view handed out
+// (TensorPtr captured by torch::from_blob's deleter, torch/adapter.cc:70-76)
+struct BatchHolder {
+  xg_batch *batch = nullptr;
+  xg_batch_view view{};
+  uint64_t key = 0;
+  ~BatchHolder() {
+    if (batch) xg_batch_release(batch);
+  }
+};
+using BatchPtr = std::shared_ptr<BatchHolder>;
+
+struct Engine {
+  Dataset ds;
+  SharedBlock *shared = nullptr;  // arch6 only
+  bool dataset_loaded = false, sampler_ready = false, trainer_ready = false, shutdown = false;
+  int worker_id = 0, device = 0;
+  size_t num_step = 0, num_local_step = 0;
+  cudaStream_t stream = nullptr;
+  // GGMS handles
+  xg_graph graph{};
+  xg_feature_store store{};
+  std::vector<void *> owned;  // device allocations freed at shutdown
+  void *d_label = nullptr;
+  const float *d_prob = nullptr, *d_prefix = nullptr;
+  const uint32_t *d_alias = nullptr;
+  std::unique_ptr<AlignedShuffler> shuffler;
+  xg_sampler *sampler = nullptr;
+  // GraphPool (graph_pool.cc:31-49) + current batch (operation.cc:366-378)
+  std::mutex mu;
+  std::condition_variable cv;
+  std::deque<BatchPtr> pool;
+  BatchPtr current;
+  std::vector<std::thread> threads;
+  bool producer_done = false;
+};
+Engine *g_engine = nullptr;
+
+Engine &engine() {
+  SAM_CHECK_MSG(g_engine != nullptr, "engine is not created: call samgraph_init or samgraph_data_init first");
+  return *g_engine;
+}
+
+void *dev_alloc(Engine &e, size_t bytes) {
+  void *p = nullptr;
+  SAM_XG(xg_device_malloc(&p, bytes));
+  e.owned.push_back(p);
+  return p;
+}
+
+// make a host range loadable from kernels (cudaHostRegister of the dataset mappings, dist_engine.cc:219-222,
+// 239-240); falls back to a pinned copy where the mapping cannot be registered (private file mappings)
+const void *pin_host(const void *p, size_t bytes) {
+  if (!p || bytes == 0) return p;
+  cudaError_t err = cudaHostRegister(const_cast<void *>(p), bytes, cudaHostRegisterDefault | cudaHostRegisterReadOnly);
+  if (err == cudaSuccess || err == cudaErrorHostMemoryAlreadyRegistered) {
+    cudaGetLastError();
+    return p;
+  }
+  cudaGetLastError();
+  err = cudaHostRegister(const_cast<void *>(p), bytes, cudaHostRegisterDefault);
+  if (err == cudaSuccess) return p;
+  cudaGetLastError();
+  void *copy = nullptr;
+  SAM_CUDA(cudaHostAlloc(&copy, bytes, cudaHostAllocDefault));
+  std::memcpy(copy, p, bytes);
+  return copy;
+}
+
+template <typename T>
+const T *to_device(Engine &e, const T *host, size_t count) {
+  if (!host || count == 0) return nullptr;
+  void *d = dev_alloc(e, count * sizeof(T));
+  SAM_CUDA(cudaMemcpy(d, host, count * sizeof(T), cudaMemcpyHostToDevice));
+  return static_cast<const T *>(d);
+}
+
+void barrier(Engine &e) {
+  if (e.shared && e.shared->num_worker > 1) {
+    int rc = pthread_barrier_wait(&e.shared->barrier);
+    SAM_CHECK(rc == 0 || rc == PTHREAD_BARRIER_SERIAL_THREAD);
+  }
+}
+
+// ---- topology: DistEngine::SampleDataCopy + DistGraph::GraphLoad (dist_engine.cc:198-244, dist_graph.cu:309-385)
+void build_topology(Engine &e) {
+  const Dataset &ds = e.ds;
+  const RunConfig &cfg = g_cfg;
+  std::memset(&e.graph, 0, sizeof(e.graph));
+  e.graph.num_node = (uint32_t)ds.num_node;
+  const bool dist = cfg.run_arch == kArch6 && cfg.use_dist_graph && e.shared != nullptr;
+  if (!dist) {  // whole CSR in this GPU's HBM (DeviceNormalGraph)
+    e.graph.num_part = 0;
+    e.graph.part_indptr[0] = to_device(e, ds.indptr, ds.num_node + 1);
+    e.graph.part_indices[0] = to_device(e, ds.indices, std::max<size_t>(ds.num_edge, 1));
+    return;
+  }
+  const uint32_t P = (uint32_t)e.shared->num_worker;
+  const uint32_t ncn = xg_num_cache_node(ds.indptr, (uint32_t)ds.num_node, cfg.dist_graph_percentage);
+  const uint32_t *h_indptr = static_cast<const uint32_t *>(pin_host(ds.indptr, (ds.num_node + 1) * 4));
+  const uint32_t *h_indices = static_cast<const uint32_t *>(pin_host(ds.indices, ds.num_edge * 4));
+  e.graph.num_part = P;
+  e.graph.num_cache_node = ncn;
+  e.graph.part_indptr[P] = h_indptr;  // slot P: the whole graph on the host (dist_graph.cu:372-383)
+  e.graph.part_indices[P] = h_indices;
+  const int w = e.worker_id;
+  std::vector<const uint32_t *> my_indptr(P, nullptr), my_indices(P, nullptr);
+  for (int k = 0; k < e.shared->num_parts[w]; ++k) {
+    const uint32_t p = (uint32_t)e.shared->part_ids[w][k];
+    const size_t rows = xg_part_num_rows(ncn, p, P);
+    auto *d_ptr = static_cast<uint32_t *>(dev_alloc(e, (rows + 1) * sizeof(uint32_t)));
+    SAM_CUDA(cudaMemsetAsync(d_ptr, 0, (rows + 1) * sizeof(uint32_t), e.stream));
+    size_t edges = 0;
+    if (rows) {
+      uint32_t *d_deg = nullptr;
+      SAM_CUDA(cudaMalloc(&d_deg, (rows + 1) * sizeof(uint32_t)));
+      SAM_CUDA(cudaMemsetAsync(d_deg, 0, (rows + 1) * sizeof(uint32_t), e.stream));
+      SAM_XG(xg_part_degrees(h_indptr, ncn, p, P, d_deg, e.stream));
+      size_t tmp_bytes = 0;
+      SAM_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, d_deg, d_ptr, (int)(rows + 1), e.stream));
+      void *tmp = nullptr;
+      SAM_CUDA(cudaMalloc(&tmp, tmp_bytes ? tmp_bytes : 16));
+      SAM_CUDA(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, d_deg, d_ptr, (int)(rows + 1), e.stream));
+      uint32_t last = 0;
+      SAM_CUDA(cudaMemcpyAsync(&last, d_ptr + rows, sizeof(uint32_t), cudaMemcpyDeviceToHost, e.stream));
+      SAM_CUDA(cudaStreamSynchronize(e.stream));
+      cudaFree(tmp);
+      cudaFree(d_deg);
+      edges = last;
+    }
+    auto *d_idx = static_cast<uint32_t *>(dev_alloc(e, std::max<size_t>(edges, 1) * sizeof(uint32_t)));
+    if (edges) SAM_XG(xg_part_copy_indices(h_indptr, h_indices, ncn, p, P, d_ptr, d_idx, e.stream));
+    SAM_CUDA(cudaStreamSynchronize(e.stream));
+    my_indptr[p] = d_ptr;
+    my_indices[p] = d_idx;
+    SAM_XG(xg_ipc_export(d_ptr, e.shared->topo_indptr[w][p]));
+    SAM_XG(xg_ipc_export(d_idx, e.shared->topo_indices[w][p]));
+  }
+  barrier(e);  // every handle is published (DistGraph::_DataIpcShare, dist_graph.cu:274-307)
+  for (uint32_t p = 0; p < P; ++p) {
+    const int owner = e.shared->access[w][p];
+    if (owner == w) {
+      SAM_CHECK(my_indptr[p] != nullptr);
+      e.graph.part_indptr[p] = my_indptr[p];
+      e.graph.part_indices[p] = my_indices[p];
+    } else {
+      void *a = nullptr, *b = nullptr;
+      SAM_XG(xg_ipc_import(e.shared->topo_indptr[owner][p], &a));
+      SAM_XG(xg_ipc_import(e.shared->topo_indices[owner][p], &b));
+      e.graph.part_indptr[p] = static_cast<const uint32_t *>(a);
+      e.graph.part_indices[p] = static_cast<const uint32_t *>(b);
+    }
+  }
+  barrier(e);
+}
+
+// ---- features: GPUCacheManager ctor + DistGraph::FeatureLoad (cuda_cache_manager_host.cc:133-254, dist_graph.cu:387-547)
+void build_feature_store(Engine &e) {
+  const Dataset &ds = e.ds;
+  const RunConfig &cfg = g_cfg;
+  std::memset(&e.store, 0, sizeof(e.store));
+  const size_t row_bytes = ds.feat_row_bytes();
+  e.store.row_bytes = row_bytes;
+  const size_t V = ds.num_node;
+  size_t n_cached = (size_t)(V * cfg.cache_percentage);
+  if (n_cached > V) n_cached = V;
+  if (n_cached < V) e.store.host = pin_host(ds.feat, V * row_bytes);  // misses: zero-copy UVA loads
+  if (n_cached == 0) return;                                          // cache_table == NULL: every row from `host`
+  const bool parted = cfg.run_arch == kArch6 && cfg.part_cache && e.shared != nullptr;
+  const uint32_t P = parted ? (uint32_t)e.shared->num_worker : 1u;
+  std::vector<uint32_t> ranks(ds.ranking, ds.ranking + n_cached);
+  if (parted) SAM_XG(xg_shuffle_cache_ranks(ranks.data(), n_cached));  // cuda_cache_manager_host.cc:162-171
+  {
+    std::vector<uint32_t> table(V, XG_EMPTY_KEY);
+    for (size_t r = 0; r < n_cached; ++r) table[ranks[r]] = (uint32_t)r;
+    e.store.cache_table = to_device(e, table.data(), V);
+  }
+  const void *h_feat = pin_host(ds.feat, V * row_bytes);
+  e.store.num_part = P;
+  const int w = e.worker_id;
+  std::vector<void *> mine(P, nullptr);
+  const int my_parts = parted ? e.shared->num_parts[w] : 1;
+  for (int k = 0; k < my_parts; ++k) {
+    const uint32_t p = parted ? (uint32_t)e.shared->part_ids[w][k] : 0u;
+    std::vector<uint32_t> ids;
+    for (size_t r = p; r < n_cached; r += P) ids.push_back(ranks[r]);  // rank r -> part r % P, row r / P
+    void *d_part = dev_alloc(e, std::max<size_t>(ids.size() * row_bytes, 16));
+    if (!ids.empty()) {
+      uint32_t *d_ids = nullptr;
+      SAM_CUDA(cudaMalloc(&d_ids, ids.size() * sizeof(uint32_t)));
+      SAM_CUDA(cudaMemcpyAsync(d_ids, ids.data(), ids.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, e.stream));
+      // CPUExtract + H2D in the reference; here the GPU gathers the rows straight out of the host mapping
+      SAM_XG(xg_extract_miss_data(d_part, h_feat, d_ids, nullptr, ids.size(), row_bytes, e.stream));
+      SAM_CUDA(cudaStreamSynchronize(e.stream));
+      cudaFree(d_ids);
+    }
+    mine[p] = d_part;
+    e.store.local_part_mask |= 1u << p;
+    if (parted) SAM_XG(xg_ipc_export(d_part, e.shared->feat[w][p]));
+  }
+  if (!parted) {
+    e.store.part[0] = mine[0];
+    return;
+  }
+  barrier(e);
+  for (uint32_t p = 0; p < P; ++p) {
+    const int owner = e.shared->access[w][p];
+    if (owner == w) {
+      e.store.part[p] = mine[p];
+    } else {
+      void *a = nullptr;
+      SAM_XG(xg_ipc_import(e.shared->feat[owner][p], &a));
+      e.store.part[p] = a;
+    }
+  }
+  barrier(e);
+}
+
+}  // namespace sam
+
+namespace sam {
+
+void create_sampler(Engine &e) {
+  if (e.sampler) return;
+  const RunConfig &cfg = g_cfg;
+  const Dataset &ds = e.ds;
+  xg_sampler_config sc{};
+  sc.num_layer = (uint32_t)cfg.num_layer;
+  SAM_CHECK(cfg.num_layer >= 1 && cfg.num_layer <= XG_MAX_LAYERS && cfg.fanout.size() >= cfg.num_layer);
+  for (size_t l = 0; l < cfg.num_layer; ++l) sc.fanout[l] = (uint32_t)cfg.fanout[l];
+  sc.batch_size = (uint32_t)cfg.batch_size;
+  sc.sample_type = cfg.sample_type;
+  sc.num_slots = 4;  // current + pooled + in flight + one held by the caller's tensors
+  sc.feat_dim = (uint32_t)ds.feat_dim;
+  sc.feat_dtype = ds.feat_dtype;
+  sc.seed = 0x58474E4Eull;  // reproducible, unlike the reference's wall-clock seed (cuda_random_states.cu:106-108)
+  if (const char *s = std::getenv("SAMGRAPH_SEED")) sc.seed = std::strtoull(s, nullptr, 0);
+  sc.stream = e.stream;
+  sc.random_walk_length = (uint32_t)cfg.random_walk_length;
+  sc.num_random_walk = (uint32_t)cfg.num_random_walk;
+  sc.random_walk_restart_prob = cfg.random_walk_restart_prob;
+  sc.prob_table = e.d_prob;
+  sc.alias_table = e.d_alias;
+  sc.prob_prefix_table = e.d_prefix;
+  SAM_XG(xg_sampler_create(&e.sampler, &e.graph, e.trainer_ready ? &e.store : nullptr, e.trainer_ready ? e.d_label : nullptr,
+                           &sc, e.device));
+}
+
+// RunSampleSubLoopOnce + RunCacheDataCopySubLoopOnce for one Task (dist_loops_arch6.cc:55-199).
+// Returns false once every epoch has been produced.
+bool produce_one(Engine &e) {
+  SAM_CHECK_MSG(e.sampler_ready, "sample_init / init has not run");
+  create_sampler(e);
+  const double t0 = now_s();
+  const uint32_t *d_seeds = nullptr;
+  size_t n = 0, epoch = 0, local_step = 0;
+  if (!e.shuffler->get_batch(e.stream, &d_seeds, &n, &epoch, &local_step)) return false;
+  const double t_shuffle = now_s() - t0;
+  // Engine::GetBatchKey(epoch, step) with the blocked global step (dist_shuffler_aligned.h:38-40, engine.h:50-54)
+  const uint64_t key = epoch * e.num_step + e.shuffler->global_step_offset + local_step;
+  auto holder = std::make_shared<BatchHolder>();
+  holder->key = key;
+  SAM_XG(xg_sampler_submit(e.sampler, d_seeds, n, 1, key, &holder->batch));
+  SAM_XG(xg_batch_wait(holder->batch, &holder->view));
+  const double t_total = now_s() - t0;
+  double edges = 0;
+  for (uint32_t l = 0; l < holder->view.num_layer; ++l) edges += (double)holder->view.num_edge[l];
+  const double feat_bytes = (double)holder->view.num_input * e.ds.feat_row_bytes();
+  g_prof.log_step(key, kLogL1NumSample, edges, false);
+  g_prof.log_step(key, kLogL1NumNode, (double)holder->view.num_input, false);
+  g_prof.log_step(key, kLogL1SampleTime, t_total, false);  // sample and extract are one fused chain: all of it
+  g_prof.log_step(key, kLogL1SampleTotalTime, t_total, false);
+  g_prof.log_step(key, kLogL2ShuffleTime, t_shuffle, false);
+  g_prof.log_step(key, kLogL2CoreSampleTime, t_total - t_shuffle, false);
+  g_prof.log_step(key, kLogL1CopyTime, 0.0, false);
+  g_prof.log_step(key, kLogL1FeatureBytes, feat_bytes, false);
+  g_prof.log_step(key, kLogL1LabelBytes, (double)holder->view.num_output * 8, false);
+  g_prof.log_epoch_add(epoch, kLogEpochSampleTime, t_total);
+  g_prof.log_epoch_add(epoch, kLogEpochSampleTotalTime, t_total);
+  g_prof.log_epoch_add(epoch, kLogEpochNumSample, edges);
+  g_prof.log_epoch_add(epoch, kLogEpochFeatureBytes, feat_bytes);
+  {
+    std::lock_guard<std::mutex> lk(e.mu);
+    e.pool.push_back(holder);  // GraphPool::Submit
+  }
+  e.cv.notify_all();
+  return true;
+}
+
+void common_device_init(Engine &e, int device) {
+  e.device = device;
+  SAM_CUDA(cudaSetDevice(device));
+  SAM_CUDA(cudaStreamCreateWithFlags(&e.stream, cudaStreamNonBlocking));
+}
+
+void sampler_side_init(Engine &e) {
+  const double t0 = now_s();
+  build_topology(e);
+  if (g_cfg.sample_type == XG_WEIGHTED_KHOP || g_cfg.sample_type == XG_WEIGHTED_KHOP_HASH_DEDUP) {
+    e.d_prob = to_device(e, e.ds.prob, e.ds.num_edge);
+    e.d_alias = to_device(e, e.ds.alias, e.ds.num_edge);
+  } else if (g_cfg.sample_type == XG_WEIGHTED_KHOP_PREFIX) {
+    e.d_prefix = to_device(e, e.ds.prefix, e.ds.num_edge);
+  }
+  e.shuffler.reset(new AlignedShuffler(e.ds.train_set, e.ds.num_train, g_cfg.num_epoch, g_cfg.batch_size,
+                                       (size_t)e.worker_id, g_cfg.num_worker));
+  SAM_CHECK(e.shuffler->num_local_step == e.num_local_step);
+  e.sampler_ready = true;
+  g_prof.init[kLogInitL1Sampler] = now_s() - t0;
+}
+
+void trainer_side_init(Engine &e) {
+  const double t0 = now_s();
+  build_feature_store(e);
+  e.d_label = const_cast<int64_t *>(to_device(e, e.ds.label, e.ds.num_node));  // labels: 8 B x V, kept in HBM
+  e.trainer_ready = true;
+  g_prof.init[kLogInitL1Trainer] = now_s() - t0;
+  g_prof.init[kLogInitL2BuildCache] = now_s() - t0;
+}
+
+void create_engine(bool shared_dataset) {
+  SAM_CHECK(g_cfg.is_configured);
+  SAM_CHECK_MSG(g_engine == nullptr, "engine already created");
+  g_engine = new Engine();
+  Engine &e = *g_engine;
+  const double t0 = now_s();
+  load_dataset(e.ds, g_cfg, shared_dataset);
+  e.dataset_loaded = true;
+  g_prof.init[kLogInitL2LoadDataset] = now_s() - t0;
+  // dist_engine.cc:139-148: steps are counted on the padded, per-worker slice
+  const size_t W = g_cfg.num_worker;
+  e.num_local_step = ((e.ds.num_train + W - 1) / W + g_cfg.batch_size - 1) / g_cfg.batch_size;
+  e.num_step = e.num_local_step * W;
+}
+
+}  // namespace sam
+
+using namespace sam;
+
+extern "C" {
+
+// operation.cc:49-326
+void samgraph_config(const char **keys, const char **vals, const size_t n) {
+  RunConfig &c = g_cfg;
+  SAM_CHECK(!c.is_configured);
+  std::unordered_map<std::string, std::string> m;
+  for (size_t i = 0; i < n; ++i) m[keys[i]] = vals[i];
+  for (const char *need : {"dataset_path", "_arch", "_sample_type", "batch_size", "num_epoch", "_cache_policy",
+                           "cache_percentage", "max_sampling_jobs", "max_copying_jobs", "omp_thread_num", "num_layer",
+                           "num_hidden", "lr", "dropout"})
+    SAM_CHECK_MSG(m.count(need) > 0, std::string("missing config key ") + need);  // operation.cc:68-81
+  c.raw = m;
+  c.dataset_path = m["dataset_path"];
+  c.run_arch = std::stoi(m["_arch"]);
+  c.sample_type = std::stoi(m["_sample_type"]);
+  c.batch_size = std::stoull(m["batch_size"]);
+  c.num_epoch = std::stoull(m["num_epoch"]);
+  c.cache_policy = std::stoi(m["_cache_policy"]);
+  c.cache_percentage = std::stod(m["cache_percentage"]);
+  c.omp_thread_num = std::stoi(m["omp_thread_num"]);
+  c.num_layer = std::stoull(m["num_layer"]);
+  switch (c.run_arch) {
+    case kArch0: case kArch1: case kArch2: case kArch3: case kArch4: case kArch7:
+      SAM_CHECK(m.count("sampler_ctx") && m.count("trainer_ctx"));
+      c.sampler_device = parse_ctx(m["sampler_ctx"]);
+      c.trainer_device = parse_ctx(m["trainer_ctx"]);
+      c.num_worker = 1;
+      // arch0's CPU sampler is the oracle, not a product path: every single-process arch samples on a GPU here
+      if (c.sampler_device < 0) c.sampler_device = c.trainer_device;
+      SAM_CHECK_MSG(c.sampler_device >= 0, "a CUDA context is required (xgnn_b200 has no CPU path)");
+      break;
+    case kArch6:
+      SAM_CHECK(m.count("num_worker"));
+      c.num_worker = std::stoull(m["num_worker"]);
+      SAM_CHECK(c.num_worker >= 1 && c.num_worker <= (size_t)kMaxWorker);
+      break;
+    default:
+      fatal(__FILE__, __LINE__, "arch " + m["_arch"] + " is a different deployment mode (arch5/arch9): out of scope");
+  }
+  if (c.sample_type != XG_RANDOM_WALK) {  // operation.cc:150-161
+    SAM_CHECK(m.count("num_fanout") && m.count("fanout"));
+    const size_t nf = std::stoull(m["num_fanout"]);
+    std::stringstream ss(m["fanout"]);
+    for (size_t i = 0; i < nf; ++i) {
+      size_t f = 0;
+      ss >> f;
+      c.fanout.push_back(f);
+    }
+  } else {  // operation.cc:162-175
+    SAM_CHECK(m.count("random_walk_length") && m.count("random_walk_restart_prob") && m.count("num_random_walk") &&
+              m.count("num_neighbor"));
+    c.random_walk_length = std::stoull(m["random_walk_length"]);
+    c.random_walk_restart_prob = std::stod(m["random_walk_restart_prob"]);
+    c.num_random_walk = std::stoull(m["num_random_walk"]);
+    c.num_neighbor = std::stoull(m["num_neighbor"]);
+    c.fanout.assign(c.num_layer, c.num_neighbor);
+  }
+  if (m.count("use_dist_graph")) {  // operation.cc:191-203
+    c.dist_graph_percentage = std::stod(m["use_dist_graph"]);
+    c.use_dist_graph = c.dist_graph_percentage > 0.0;
+  }
+  if (m.count("part_cache") && m["part_cache"] == "True") {
+    SAM_CHECK_MSG(c.run_arch == kArch6, "partition cache can only be used in arch6");  // operation.cc:205-211
+    c.part_cache = true;
+  }
+  if (m.count("use_ics22_song_solver") && m["use_ics22_song_solver"] == "True")
+    fatal(__FILE__, __LINE__, "the ICS'22 clique placement is a comparison baseline: out of scope");
+  c.gpu_extract = m.count("gpu_extract") && m["gpu_extract"] == "True";
+  if (m.count("unified_memory") && m["unified_memory"] == "True")
+    fatal(__FILE__, __LINE__, "unified-memory sampling (arch9 / UM) is out of scope");
+  c.is_configured = true;
+}
+
+void samgraph_init(void) {  // operation.cc:328-334 (single process)
+  SAM_CHECK(g_cfg.is_configured);
+  SAM_CHECK_MSG(g_cfg.run_arch != kArch6, "arch6 starts with samgraph_data_init (then fork, sample_init, train_init)");
+  create_engine(false);
+  Engine &e = engine();
+  common_device_init(e, g_cfg.sampler_device);
+  sampler_side_init(e);
+  trainer_side_init(e);
+}
+
+void samgraph_data_init(void) {  // operation.cc:509-533: parent process, BEFORE fork; no CUDA call in here
+  SAM_CHECK(g_cfg.is_configured);
+  create_engine(true);
+  Engine &e = engine();
+  if (g_cfg.run_arch == kArch6) {
+    void *mem = ::mmap(nullptr, sizeof(SharedBlock), PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+    SAM_CHECK(mem != MAP_FAILED);
+    e.shared = new (mem) SharedBlock();
+    std::memset(static_cast<void *>(e.shared), 0, sizeof(SharedBlock));
+    const int W = (int)g_cfg.num_worker;
+    e.shared->num_worker = W;
+    pthread_barrierattr_t attr;
+    pthread_barrierattr_init(&attr);
+    pthread_barrierattr_setpshared(&attr, PTHREAD_PROCESS_SHARED);  // dist_graph.cu:619-630
+    SAM_CHECK(pthread_barrier_init(&e.shared->barrier, &attr, (unsigned)W) == 0);
+    // placement: PartitionSolver over the link matrix.  SAMGRAPH_TOPO_MATRIX = file with W rows of W GB/s numbers
+    // (0 = no P2P path); default = all-to-all (NVSwitch), for which the solver returns the identity placement.
+    std::vector<double> bw((size_t)W * W, 770.0);
+    for (int i = 0; i < W; ++i) bw[(size_t)i * W + i] = 6500.0;
+    if (const char *f = std::getenv("SAMGRAPH_TOPO_MATRIX")) {
+      std::ifstream in(f);
+      SAM_CHECK_MSG(in.is_open(), std::string("cannot open ") + f);
+      for (auto &x : bw) SAM_CHECK_MSG(static_cast<bool>(in >> x), "SAMGRAPH_TOPO_MATRIX is too short");
+    }
+    std::vector<int> nparts(W), parts((size_t)W * W), access((size_t)W * W);
+    SAM_XG(xg_partition_solve(bw.data(), W, nparts.data(), parts.data(), access.data()));
+    for (int g = 0; g < W; ++g) {
+      e.shared->num_parts[g] = nparts[g];
+      for (int p = 0; p < W; ++p) {
+        e.shared->part_ids[g][p] = parts[(size_t)g * W + p];
+        e.shared->access[g][p] = access[(size_t)g * W + p];
+      }
+    }
+  }
+}
+
+void samgraph_sample_init(int worker_id, const char *ctx) {  // operation.cc:535-540 -> DistEngine::SampleInit
+  Engine &e = engine();
+  SAM_CHECK(g_cfg.run_arch == kArch6 && worker_id >= 0 && (size_t)worker_id < g_cfg.num_worker);
+  e.worker_id = worker_id;
+  common_device_init(e, parse_ctx(ctx));
+  sampler_side_init(e);
+}
+
+void samgraph_train_init(int worker_id, const char *ctx) {  // operation.cc:549-554 -> DistEngine::TrainInit
+  Engine &e = engine();
+  SAM_CHECK(g_cfg.run_arch == kArch6 && worker_id == e.worker_id);
+  SAM_CHECK_MSG(parse_ctx(ctx) == e.device, "arch6 samples and trains on the same GPU (dist_engine.cc:589-700)");
+  trainer_side_init(e);
+}
+
+void samgraph_um_sample_init(int) { fatal(__FILE__, __LINE__, "samgraph_um_sample_init belongs to arch9 (UM sampler): out of scope"); }
+void samgraph_switch_init(int, const char *, double) { fatal(__FILE__, __LINE__, "samgraph_switch_init belongs to arch5's switcher: out of scope"); }
+
+void samgraph_sample_once(void) {  // operation.cc:380
+  Engine &e = engine();
+  if (!produce_one(e)) {
+    std::lock_guard<std::mutex> lk(e.mu);
+    e.producer_done = true;
+  }
+}
+
+static void producer_loop(Engine *e, long count) {
+  SAM_CUDA(cudaSetDevice(e->device));
+  for (long i = 0; count < 0 || i < count; ++i) {
+    {  // GraphPool::Full(): bounded look-ahead (graph_pool.h: max_copying_jobs)
+      std::unique_lock<std::mutex> lk(e->mu);
+      e->cv.wait(lk, [&] { return e->pool.size() < 2 || e->shutdown; });
+      if (e->shutdown) return;
+    }
+    if (!produce_one(*e)) break;
+  }
+  std::lock_guard<std::mutex> lk(e->mu);
+  e->producer_done = true;
+  e->cv.notify_all();
+}
+
+void samgraph_start(void) {  // operation.cc:336-345: background producer for every epoch
+  Engine &e = engine();
+  SAM_CHECK(e.sampler_ready && !e.shutdown);
+  e.threads.emplace_back(producer_loop, &e, -1L);
+}
+
+void samgraph_extract_start(int count) {  // operation.cc:556-559 -> DistEngine::StartExtract
+  Engine &e = engine();
+  SAM_CHECK(e.sampler_ready && !e.shutdown);
+  e.threads.emplace_back(producer_loop, &e, (long)count);
+}
+
+uint64_t samgraph_get_next_batch(void) {  // operation.cc:366-378
+  Engine &e = engine();
+  std::unique_lock<std::mutex> lk(e.mu);
+  e.current.reset();  // SetGraphBatch(nullptr): the previous batch is dropped unless a tensor still holds it
+  e.cv.notify_all();
+  e.cv.wait(lk, [&] { return !e.pool.empty() || e.shutdown; });
+  SAM_CHECK(!e.pool.empty());
+  e.current = e.pool.front();
+  e.pool.pop_front();
+  e.cv.notify_all();
+  return e.current->key;
+}
+
+static BatchHolder &current_batch() {
+  Engine &e = engine();
+  SAM_CHECK_MSG(e.current != nullptr, "no current batch: call samgraph_get_next_batch first");
+  return *e.current;
+}
+size_t samgraph_get_graph_num_src(uint64_t, int g) { return current_batch().view.num_src[g]; }
+size_t samgraph_get_graph_num_dst(uint64_t, int g) { return current_batch().view.num_dst[g]; }
+size_t samgraph_get_graph_num_edge(uint64_t, int g) { return current_batch().view.num_edge[g]; }
+
+size_t samgraph_num_epoch(void) { return g_cfg.num_epoch; }
+size_t samgraph_steps_per_epoch(void) { return engine().num_step; }
+size_t samgraph_num_local_step(void) { return engine().num_local_step; }
+size_t samgraph_num_class(void) { return engine().ds.num_class; }
+size_t samgraph_feat_dim(void) { return engine().ds.feat_dim; }
+
+void samgraph_shutdown(void) {  // operation.cc:397-403
+  Engine &e = engine();
+  {
+    std::lock_guard<std::mutex> lk(e.mu);
+    e.shutdown = true;
+  }
+  e.cv.notify_all();
+  for (auto &t : e.threads) t.join();
+  e.threads.clear();
+  e.pool.clear();
+  e.current.reset();
+  if (e.stream) cudaStreamSynchronize(e.stream);
+}
+
+int samgraph_wait_one_child(void) {  // operation.cc:573-584
+  int st = 0;
+  pid_t pid = ::waitpid(-1, &st, 0);
+  if (pid < 0) return 1;
+  if (WIFSIGNALED(st)) return 1;
+  return WEXITSTATUS(st) != 0 ? 1 : 0;
+}
+
+void samgraph_forward_barrier(void) { barrier(engine()); }
+
+}  // extern "C"
+
+extern "C" {
+
+// ---- Profiler surface (operation.cc:405-500) ---------------------------------------------------------
+static uint64_t batch_key(uint64_t epoch, uint64_t step) { return epoch * engine().num_step + step; }  // engine.h:50-54
+
+void samgraph_log_step(uint64_t epoch, uint64_t step, int item, double val) {
+  SAM_CHECK(item >= 0 && item < kNumLogStepItems);
+  g_prof.log_step(batch_key(epoch, step), item, val, false);
+}
+void samgraph_log_step_by_key(uint64_t key, int item, double val) {
+  SAM_CHECK(item >= 0 && item < kNumLogStepItems);
+  g_prof.log_step(key, item, val, false);
+}
+void samgraph_log_step_add(uint64_t epoch, uint64_t step, int item, double val) {
+  SAM_CHECK(item >= 0 && item < kNumLogStepItems);
+  g_prof.log_step(batch_key(epoch, step), item, val, true);
+}
+void samgraph_log_epoch_add(uint64_t epoch, int item, double val) {
+  SAM_CHECK(item >= 0 && item < kNumLogEpochItems);
+  g_prof.log_epoch_add(epoch, item, val);
+}
+double samgraph_get_log_init_value(int item) {
+  SAM_CHECK(item >= 0 && item < kNumLogInitItems);
+  return g_prof.init[item];
+}
+double samgraph_get_log_step_value(uint64_t epoch, uint64_t step, int item) {
+  SAM_CHECK(item >= 0 && item < kNumLogStepItems);
+  return g_prof.get_step(batch_key(epoch, step), item);
+}
+double samgraph_get_log_step_value_by_key(uint64_t key, int item) {
+  SAM_CHECK(item >= 0 && item < kNumLogStepItems);
+  return g_prof.get_step(key, item);
+}
+double samgraph_get_log_epoch_value(uint64_t epoch, int item) {
+  SAM_CHECK(item >= 0 && item < kNumLogEpochItems);
+  return g_prof.get_epoch(epoch, item);
+}
+
+void samgraph_report_init(void) {
+  std::printf("    [Init Profiler Level 1] load dataset %.4f | sampler %.4f | trainer %.4f\n",
+              g_prof.init[kLogInitL2LoadDataset], g_prof.init[kLogInitL1Sampler], g_prof.init[kLogInitL1Trainer]);
+  std::fflush(stdout);
+}
+void samgraph_report_step(uint64_t epoch, uint64_t step) {
+  const uint64_t k = batch_key(epoch, step);
+  std::printf("    [Step(%llu) Profiler Level 1 E%llu S%llu] sample+extract %.4f | nodes %.0f | samples %.0f\n",
+              (unsigned long long)k, (unsigned long long)epoch, (unsigned long long)step, g_prof.get_step(k, kLogL1SampleTime),
+              g_prof.get_step(k, kLogL1NumNode), g_prof.get_step(k, kLogL1NumSample));
+}
+void samgraph_report_step_average(uint64_t epoch, uint64_t step) {
+  samgraph_report_step(epoch, step);
+  std::fflush(stdout);
+}
+void samgraph_report_epoch(uint64_t epoch) {
+  std::printf("    [Epoch Profiler E%llu] sample+extract %.4f | samples %.0f | feature bytes %.0f\n",
+              (unsigned long long)epoch, g_prof.get_epoch(epoch, kLogEpochSampleTime),
+              g_prof.get_epoch(epoch, kLogEpochNumSample), g_prof.get_epoch(epoch, kLogEpochFeatureBytes));
+}
+void samgraph_report_epoch_average(uint64_t epoch) {
+  samgraph_report_epoch(epoch);
+  std::fflush(stdout);
+}
+void samgraph_report_node_access(void) {}  // SAMGRAPH_LOG_NODE_ACCESS statistics: not collected
+
+// Chrome-trace style begin/end marks (profiler.cc TraceStepBegin/End, DumpTrace)
+namespace {
+struct TraceEvent { uint64_t key; int item; uint64_t begin_us, end_us; };
+std::mutex g_trace_mu;
+std::vector<TraceEvent> g_trace;
+uint64_t now_us() {
+  return (uint64_t)std::chrono::duration_cast<std::chrono::microseconds>(std::chrono::system_clock::now().time_since_epoch()).count();
+}
+}  // namespace
+void samgraph_trace_step_begin(uint64_t key, int item, uint64_t ts) {
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  g_trace.push_back({key, item, ts, 0});
+}
+void samgraph_trace_step_end(uint64_t key, int item, uint64_t ts) {
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  for (auto it = g_trace.rbegin(); it != g_trace.rend(); ++it)
+    if (it->key == key && it->item == item && it->end_us == 0) {
+      it->end_us = ts;
+      return;
+    }
+}
+void samgraph_trace_step_begin_now(uint64_t key, int item) { samgraph_trace_step_begin(key, item, now_us()); }
+void samgraph_trace_step_end_now(uint64_t key, int item) { samgraph_trace_step_end(key, item, now_us()); }
+void samgraph_dump_trace(void) {
+  std::lock_guard<std::mutex> lk(g_trace_mu);
+  std::fprintf(stderr, "[\n");
+  for (const auto &t : g_trace)
+    std::fprintf(stderr, "{\"name\":\"item%d\",\"ph\":\"X\",\"pid\":0,\"tid\":%d,\"ts\":%llu,\"dur\":%llu,\"args\":{\"key\":%llu}},\n",
+                 t.item, t.item, (unsigned long long)t.begin_us,
+                 (unsigned long long)(t.end_us > t.begin_us ? t.end_us - t.begin_us : 0), (unsigned long long)t.key);
+  std::fprintf(stderr, "]\n");
+}
+
+// ---- tensor views (torch/adapter.cc:62-193) -----------------------------------------------------------
+void samgraph_get_graph_tensor(uint64_t key, int which, int layer, samgraph_tensor_view *out) {
+  SAM_CHECK(out != nullptr);
+  Engine &e = engine();
+  std::memset(out, 0, sizeof(*out));
+  out->ndim = 1;
+  if (which == SAMGRAPH_TENSOR_DATASET_FEAT || which == SAMGRAPH_TENSOR_DATASET_LABEL) {
+    out->device = -1;
+    if (which == SAMGRAPH_TENSOR_DATASET_FEAT) {
+      out->data = const_cast<void *>(e.ds.feat);
+      out->ndim = 2;
+      out->shape[0] = (int64_t)e.ds.num_node;
+      out->shape[1] = (int64_t)e.ds.feat_dim;
+      out->dtype = e.ds.feat_dtype;
+    } else {
+      out->data = const_cast<int64_t *>(e.ds.label);
+      out->shape[0] = (int64_t)e.ds.num_node;
+      out->dtype = XG_I64;
+    }
+    return;
+  }
+  BatchPtr cur;
+  {
+    std::lock_guard<std::mutex> lk(e.mu);
+    cur = e.current;
+  }
+  SAM_CHECK_MSG(cur != nullptr, "no current batch");
+  SAM_CHECK_MSG(key == cur->key, "key does not name the current batch (CHECK_EQ, torch/adapter.cc:68)");
+  const xg_batch_view &v = cur->view;
+  out->device = e.device;
+  out->dtype = XG_I32;
+  switch (which) {
+    case SAMGRAPH_TENSOR_FEAT:
+      SAM_CHECK_MSG(v.input_feat != nullptr, "no features: train_init has not run");
+      out->data = const_cast<void *>(v.input_feat);
+      out->ndim = 2;
+      out->shape[0] = v.num_input;
+      out->shape[1] = (int64_t)e.ds.feat_dim;
+      out->dtype = e.ds.feat_dtype;
+      break;
+    case SAMGRAPH_TENSOR_LABEL:
+      SAM_CHECK_MSG(v.output_label != nullptr, "no labels: train_init has not run");
+      out->data = const_cast<int64_t *>(v.output_label);
+      out->shape[0] = v.num_output;
+      out->dtype = XG_I64;
+      break;
+    case SAMGRAPH_TENSOR_ROW: case SAMGRAPH_TENSOR_COL: case SAMGRAPH_TENSOR_DATA: {
+      SAM_CHECK(layer >= 0 && (uint32_t)layer < v.num_layer);
+      const uint32_t *p = which == SAMGRAPH_TENSOR_ROW ? v.row[layer] : which == SAMGRAPH_TENSOR_COL ? v.col[layer] : v.data[layer];
+      SAM_CHECK_MSG(p != nullptr || v.num_edge[layer] == 0, "this sampler produces no edge data");
+      out->data = const_cast<uint32_t *>(p);
+      out->shape[0] = (int64_t)v.num_edge[layer];
+      break;
+    }
+    case SAMGRAPH_TENSOR_INPUT_NODES:
+      out->data = const_cast<uint32_t *>(v.input_nodes);
+      out->shape[0] = v.num_input;
+      break;
+    case SAMGRAPH_TENSOR_OUTPUT_NODES:
+      out->data = const_cast<uint32_t *>(v.output_nodes);
+      out->shape[0] = v.num_output;
+      break;
+    default:
+      fatal(__FILE__, __LINE__, "unknown tensor id");
+  }
+  out->owner = new BatchPtr(cur);  // the view keeps the batch (and its slot) alive, like from_blob's deleter
+}
+
+void samgraph_tensor_release(void *owner) {
+  if (owner) delete static_cast<BatchPtr *>(owner);
+}
+
+}  // extern "C"
