@@ -313,6 +313,10 @@ int xg_ipc_import(const unsigned char handle[64], void **out);
 int xg_ipc_close(void *p);
 int xg_enable_peer_access(int device, int peer);
 
+/* DistAlignedShuffler::ReShuffle, dist/dist_shuffler_aligned.cc:75-121: one epoch's Fisher-Yates pass with
+ * std::default_random_engine(seed = epoch), in place over the padded train set (host memory).  The engine
+ * applies it epoch after epoch to the same array, as the reference does. */
+int xg_aligned_shuffle_epoch(uint32_t *h_data, size_t n, uint64_t epoch);
 /* PartitionSolver::solve, cuda/dist_graph.cu:728-777 (search: :40-222; standalone twin
  * utility/nvlink_placement_solver/solver.cc).  bandwidth = num_gpu x num_gpu row-major GB/s, 0 = no P2P
  * path (the diagonal is the local bandwidth).  Outputs, all num_gpu x num_gpu row-major ints except

@@ -3,6 +3,7 @@ CPU code (oracle/_ref/libxgnn_ref.so).  TEST INFRASTRUCTURE -- never imported by
 from __future__ import annotations
 
 import ctypes
+import sys
 from ctypes import POINTER, c_double, c_int, c_size_t, c_uint32, c_uint64, c_void_p
 from pathlib import Path
 
@@ -309,3 +310,36 @@ if ref is not None:
             ns, nd = np.empty(max(len(src), 1), np.uint32), np.empty(max(len(src), 1), np.uint32)
             ref.ref_hashtable_map_edges(self.h, src, dst, len(src), ns, nd)
             return ns[: len(src)], nd[: len(src)]
+
+
+# the engine with the non-uniform samplers: replay the Philox words layer by layer (salt = kSampleSalt + layer)
+def minibatch_ext(g, seeds, fan, sample_type, seed, batch_key, rw=None):
+    import philox
+    O = sys.modules[__name__]
+    L = len(fan)
+    table = O.Table(200000)
+    table.populate(seeds)
+    cur = seeds.copy()
+    out = {"row": [None] * L, "col": [None] * L, "data": [None] * L, "num_src": [0] * L, "num_dst": [0] * L}
+    for l in range(L - 1, -1, -1):
+        salt = philox.SALT + l
+        n = len(cur)
+        if sample_type == 3:
+            Lw, p, W = rw
+            src, dst, cnt = O.random_walk_topk(g["indptr"], g["indices"], cur, Lw, p, W, fan[l],
+                                               philox.words_walks(seed, batch_key, n, W, Lw, salt=salt))
+            out["data"][l] = cnt
+        elif sample_type == 6:
+            src, dst = O.sample_weighted_hash_dedup(g["indptr"], g["indices"], cur, fan[l],
+                                                    philox.words_slots(seed, batch_key, n, 16 * fan[l], c3=1, salt=salt),
+                                                    g["prob"], g["alias"])
+        else:
+            src, dst = O.sample_with_replacement(sample_type, g["indptr"], g["indices"], cur, fan[l],
+                                                 philox.words_slots(seed, batch_key, n, fan[l], salt=salt),
+                                                 prob=g["prob"], alias=g["alias"], prefix=g["prefix"])
+        table.populate(dst)
+        out["col"][l], out["row"][l] = table.map_edges(src, dst)
+        out["num_dst"][l], out["num_src"][l] = n, table.num_items()
+        cur = table.unique()
+    out["input_nodes"] = cur
+    return out

@@ -104,3 +104,56 @@ def prefix_table(indptr, weights):
         if e > b:
             out[b:e] = np.cumsum(weights[b:e] / weights[b:e].sum()).astype(np.float32)
     return out
+
+
+def write_dataset(path, indptr, indices, feat, label, train, num_class=47, valid=None, test=None, weights=None,
+                  feat_dtype_name=None):
+    """the reference's on-disk format (samgraph/common/engine.cc:109-443, constant.cc:23-51, datagen/README.md)"""
+    import os
+    os.makedirs(path, exist_ok=True)
+    valid = np.zeros(0, np.uint32) if valid is None else valid
+    test = np.zeros(0, np.uint32) if test is None else test
+    meta = {"NUM_NODE": len(indptr) - 1, "NUM_EDGE": int(indptr[-1]), "FEAT_DIM": feat.shape[1], "NUM_CLASS": num_class,
+            "NUM_TRAIN_SET": len(train), "NUM_VALID_SET": len(valid), "NUM_TEST_SET": len(test)}
+    with open(os.path.join(path, "meta.txt"), "w") as f:
+        for k, v in meta.items():
+            f.write(f"{k} {v}\n")
+        if feat_dtype_name:
+            f.write(f"FEAT_DATA_TYPE {feat_dtype_name}\n")
+    indptr.astype(np.uint32).tofile(os.path.join(path, "indptr.bin"))
+    indices.astype(np.uint32).tofile(os.path.join(path, "indices.bin"))
+    np.ascontiguousarray(feat).tofile(os.path.join(path, "feat.bin"))
+    label.astype(np.uint64).tofile(os.path.join(path, "label.bin"))
+    train.astype(np.uint32).tofile(os.path.join(path, "train_set.bin"))
+    valid.astype(np.uint32).tofile(os.path.join(path, "valid_set.bin"))
+    test.astype(np.uint32).tofile(os.path.join(path, "test_set.bin"))
+    degree_rank(indptr).tofile(os.path.join(path, "cache_by_degree.bin"))
+    if weights is not None:
+        prob, alias = alias_tables(indptr, indices, weights)
+        prob.tofile(os.path.join(path, "prob_table.bin"))
+        alias.tofile(os.path.join(path, "alias_table.bin"))
+        prefix_table(indptr, weights).tofile(os.path.join(path, "prob_prefix_table.bin"))
+
+
+def minstd_shuffle_epoch(data: np.ndarray, epoch: int) -> np.ndarray:
+    """Pure-Python restatement of DistAlignedShuffler::ReShuffle (dist/dist_shuffler_aligned.cc:86-109) on top of
+    libstdc++'s std::default_random_engine (= minstd_rand0: x <- 16807 x mod 2^31-1, seed 0 -> 1) and its
+    std::uniform_int_distribution downscaling (bits/uniform_int_dist.h: reject above uerange * scaling, divide)."""
+    M = 2147483647
+    x = epoch % M or 1
+    v = data.copy()
+    n = len(v)
+    urng_range = (M - 1) - 1  # max() - min() = 2147483646 - 1
+    for i in range(n - 1):
+        uerange = (n - 1 - i) + 1
+        assert uerange - 1 < urng_range
+        scaling = urng_range // uerange
+        past = uerange * scaling
+        while True:
+            x = (x * 16807) % M
+            ret = x - 1
+            if ret < past:
+                break
+        j = i + ret // scaling
+        v[i], v[j] = v[j], v[i]
+    return v

@@ -148,35 +148,7 @@ def test_slots_exhausted_is_reported(ops, small):
 
 
 # ---- the engine with the non-uniform samplers: replay the Philox words through the oracle, layer by layer ----
-def oracle_minibatch_ext(g, seeds, fan, sample_type, seed, batch_key, rw=None):
-    import philox
-    L = len(fan)
-    table = O.Table(200000)
-    table.populate(seeds)
-    cur = seeds.copy()
-    out = {"row": [None] * L, "col": [None] * L, "data": [None] * L, "num_src": [0] * L, "num_dst": [0] * L}
-    for l in range(L - 1, -1, -1):
-        salt = philox.SALT + l
-        n = len(cur)
-        if sample_type == 3:
-            Lw, p, W = rw
-            src, dst, cnt = O.random_walk_topk(g["indptr"], g["indices"], cur, Lw, p, W, fan[l],
-                                               philox.words_walks(seed, batch_key, n, W, Lw, salt=salt))
-            out["data"][l] = cnt
-        elif sample_type == 6:
-            src, dst = O.sample_weighted_hash_dedup(g["indptr"], g["indices"], cur, fan[l],
-                                                    philox.words_slots(seed, batch_key, n, 16 * fan[l], c3=1, salt=salt),
-                                                    g["prob"], g["alias"])
-        else:
-            src, dst = O.sample_with_replacement(sample_type, g["indptr"], g["indices"], cur, fan[l],
-                                                 philox.words_slots(seed, batch_key, n, fan[l], salt=salt),
-                                                 prob=g["prob"], alias=g["alias"], prefix=g["prefix"])
-        table.populate(dst)
-        out["col"][l], out["row"][l] = table.map_edges(src, dst)
-        out["num_dst"][l], out["num_src"][l] = n, table.num_items()
-        cur = table.unique()
-    out["input_nodes"] = cur
-    return out
+oracle_minibatch_ext = O.minibatch_ext
 
 
 @pytest.fixture(scope="module")

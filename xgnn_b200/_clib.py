@@ -169,6 +169,7 @@ _sig("xg_ipc_export", c_int, c_void_p, c_void_p)
 _sig("xg_ipc_import", c_int, c_void_p, POINTER(c_void_p))
 _sig("xg_ipc_close", c_int, c_void_p)
 _sig("xg_enable_peer_access", c_int, c_int, c_int)
+_sig("xg_aligned_shuffle_epoch", c_int, c_void_p, c_size_t, c_uint64)
 _sig("xg_partition_solve", c_int, c_void_p, c_int, c_void_p, c_void_p, c_void_p)
 _sig("xg_detect_topology", c_int, c_int, c_void_p)
 _sig("xg_predict_num_nodes", c_size_t, c_size_t, POINTER(c_uint32), c_size_t)

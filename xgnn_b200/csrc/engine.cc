@@ -612,7 +612,7 @@ void create_sampler(Engine &e) {
   for (size_t l = 0; l < cfg.num_layer; ++l) sc.fanout[l] = (uint32_t)cfg.fanout[l];
   sc.batch_size = (uint32_t)cfg.batch_size;
   sc.sample_type = cfg.sample_type;
-  sc.num_slots = 4;  // current + pooled + in flight + one held by the caller's tensors
+  sc.num_slots = 6;  // current + 2 pooled + in flight + two still referenced by the caller's tensors
   sc.feat_dim = (uint32_t)ds.feat_dim;
   sc.feat_dtype = ds.feat_dtype;
   sc.seed = 0x58474E4Eull;  // reproducible, unlike the reference's wall-clock seed (cuda_random_states.cu:106-108)
@@ -642,7 +642,13 @@ bool produce_one(Engine &e) {
   const uint64_t key = epoch * e.num_step + e.shuffler->global_step_offset + local_step;
   auto holder = std::make_shared<BatchHolder>();
   holder->key = key;
-  SAM_XG(xg_sampler_submit(e.sampler, d_seeds, n, 1, key, &holder->batch));
+  // every slot may still be referenced by tensors the caller holds (from_blob semantics): wait for one to die
+  for (int spins = 0;; ++spins) {
+    const int rc = xg_sampler_submit(e.sampler, d_seeds, n, 1, key, &holder->batch);
+    if (rc == XG_OK) break;
+    SAM_CHECK_MSG(rc == XG_ERR_CAPACITY && spins < 300000, std::string("xg_sampler_submit: ") + xg_last_error());
+    std::this_thread::sleep_for(std::chrono::microseconds(100));
+  }
   SAM_XG(xg_batch_wait(holder->batch, &holder->view));
   const double t_total = now_s() - t0;
   double edges = 0;
@@ -1116,3 +1122,13 @@ void samgraph_tensor_release(void *owner) {
 }
 
 }  // extern "C"
+
+/* host-only hook: one epoch of DistAlignedShuffler::ReShuffle (dist/dist_shuffler_aligned.cc:75-121) applied in
+ * place to `data` (already padded); lets the CPU test suite pin the permutation without a GPU */
+extern "C" int xg_aligned_shuffle_epoch(uint32_t *data, size_t n, uint64_t epoch) {
+  if (!data && n) return XG_ERR_INVALID;
+  std::vector<uint32_t> v(data, data + n);
+  sam::AlignedShuffler::shuffle_epoch(v, (size_t)epoch);
+  std::copy(v.begin(), v.end(), data);
+  return XG_OK;
+}
