@@ -348,7 +348,7 @@ def run_xgnn(args):
         num_edge = st.local["num_local_edge"]
     t_build = time.perf_counter() - t_build
 
-    stream = torch.cuda.Stream()
+    stream = torch.cuda.Stream(priority=-1)  # sample phase: short latency-bound kernels, scheduled first
     sm = ops.MinibatchSampler(st.graph, FANOUT, args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
                               label=st.label, seed=2024, num_slots=3, device=local, stream=stream)
     total = args.warmup + args.steps
@@ -389,7 +389,7 @@ def run_xgnn(args):
     launches0 = ops.launch_count()
     ev0.record(stream)
     edges, rows = run(args.warmup, args.steps, d_flat, True)
-    ev1.record(stream)
+    ev1.record(sm.extract_stream)  # every batch ends on the extract stream (its last kernels + the count read-back)
     barrier()
     ms = ev0.elapsed_time(ev1)
     launches = ops.launch_count() - launches0

@@ -210,6 +210,8 @@ int xg_combine_cache_data(void *d_out, const xg_feature_store *store, const uint
 #define XG_MAX_LAYERS 8
 #define XG_SAMPLER_NO_GRAPH 1u /* flags: launch the kernels one by one instead of replaying a graph */
 #define XG_SAMPLER_STAGE_TIMING 2u /* flags: (implies NO_GRAPH) CUDA events around every stage */
+#define XG_SAMPLER_SINGLE_STREAM 4u /* flags: sample and extract phases on ONE stream (default: the extract phase of
+                                       batch i runs on its own stream while batch i+1 is sampled) */
 
 /* stages of one minibatch, for xg_batch_stage_ms */
 enum {
@@ -282,6 +284,12 @@ int xg_batch_wait(xg_batch *b, xg_batch_view *view);
 int xg_batch_release(xg_batch *b);
 /* stream the sampler enqueues on (for events) and kernels per minibatch (for launch accounting) */
 void *xg_sampler_stream(xg_sampler *s);
+/* stream of the extract phase (feature/label gather, count read-back); == xg_sampler_stream in single-stream
+   mode. A batch is complete when xg_batch_wait returns; for stream-ordered timing record on this stream. */
+void *xg_sampler_extract_stream(xg_sampler *s);
+/* diagnostics (env XG_TIMELINE=1 at sampler creation): device timestamps, in ms since the sampler was created,
+   of {sample phase begin, sample phase end, extract phase begin, extract phase end} of a finished batch */
+int xg_batch_timeline(xg_batch *b, float ms[4]);
 uint32_t xg_sampler_launches_per_batch(xg_sampler *s);
 /* device time of one stage of a finished batch (sampler created with XG_SAMPLER_STAGE_TIMING);
  * `layer` is ignored for the stages that are not per layer */

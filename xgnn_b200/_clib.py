@@ -153,6 +153,8 @@ _sig("xg_sampler_submit", c_int, c_void_p, c_void_p, c_size_t, c_int, c_uint64, 
 _sig("xg_batch_wait", c_int, c_void_p, POINTER(XgBatchView))
 _sig("xg_batch_release", c_int, c_void_p)
 _sig("xg_sampler_stream", c_void_p, c_void_p)
+_sig("xg_sampler_extract_stream", c_void_p, c_void_p)
+_sig("xg_batch_timeline", c_int, c_void_p, POINTER(ctypes.c_float))
 _sig("xg_sampler_launches_per_batch", c_uint32, c_void_p)
 _sig("xg_batch_stage_ms", c_int, c_void_p, c_int, c_int, POINTER(ctypes.c_float))
 _sig("xg_synth_degrees", c_int, c_void_p, c_uint64, c_uint64, c_size_t, c_uint64, c_double, c_uint32, c_void_p)

@@ -31,6 +31,23 @@ template <> struct Vec<4> { using T = int; };
 template <> struct Vec<2> { using T = short; };
 template <> struct Vec<1> { using T = char; };
 
+// Feature rows are touched once per batch and the batch's rows (GBs) dwarf the 126 MB L2: mark them
+// evict-first so the stream does not push the hash table and the hot CSR lines of the sample phase out of L2.
+__device__ __forceinline__ uint64_t l2_evict_first_policy() {
+  uint64_t pol;
+  asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+  return pol;
+}
+__device__ __forceinline__ int4 ld_stream_hint(const int4 *p, uint64_t pol) {
+  int4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.s32 {%0,%1,%2,%3}, [%4], %5;"
+               : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p), "l"(pol));
+  return r;
+}
+__device__ __forceinline__ void st_stream_hint(int4 *p, const int4 &v, uint64_t pol) {
+  asm volatile("st.global.L1::no_allocate.L2::cache_hint.v4.s32 [%0], {%1,%2,%3,%4}, %5;" ::"l"(p), "r"(v.x),
+               "r"(v.y), "r"(v.z), "r"(v.w), "l"(pol) : "memory");
+}
 template <typename T> __device__ __forceinline__ T ld_stream(const T *p) { return *p; }
 template <> __device__ __forceinline__ int4 ld_stream<int4>(const int4 *p) {
   int4 r;
@@ -169,6 +186,167 @@ gather_rows_kernel(const xg_feature_store st, int mode, const uint32_t *__restri
   }
 }
 
+// ---- low-footprint variant: rows staged through a per-warp shared-memory ring with cp.async -------------
+// Same routing and the same flat 16-byte-chunk walk as gather_rows_kernel, but the bytes in flight sit in
+// shared memory (LDGSTS: global -> smem without a register round trip) instead of in registers:
+//   * one CTA of 8 warps per SM keeps kRingStages x 2 KB per warp = 96 KB per SM in flight (Little: 6.5 TB/s x
+//     ~800 ns / 148 SMs = 35 KB per SM), with ~40 registers per thread;
+//   * so the SM's register file and warp slots stay free for the NEXT batch's sample phase, which the engine
+//     runs concurrently on its own stream (pipeline.cu) - the register-staged kernel needs the whole register
+//     file (4 CTAs x 256 threads x 64 registers) to cover the same latency and therefore runs alone.
+// Two warp-uniform cursors walk the warp's groups: `issue` starts stage copies, `drain` (kRingStages - 1
+// stages behind) moves finished stages smem -> global with 128-bit LDS/STG.  A stage is 128 chunks (4 per
+// lane) of one 32-row group; the last stage of a group may be partial.
+constexpr int kRingWarps = 8;
+constexpr int kStageChunks = 128;  // 2 KB
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gsrc, uint64_t pol) {
+  const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(d), "l"(gsrc), "l"(pol) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+struct GroupCursor {   // warp-uniform position + this lane's walker for chunk (stage * 128 + u * 32 + lane)
+  uint32_t g;          // group index
+  uint32_t stage;      // stage within the group
+  uint32_t rows;       // rows in the group (<= 32)
+  uint32_t row, col;   // walker: row / column (in chunks) of this lane's next chunk
+};
+
+template <int STAGES>
+__global__ void __launch_bounds__(kRingWarps * 32)
+gather_rows_ring_kernel(const xg_feature_store st, int mode, const uint32_t *__restrict__ src_idx,
+                        const uint32_t *__restrict__ dst_idx, size_t num_rows_max,
+                        const uint32_t *__restrict__ d_num_rows, uint32_t cpr, char *__restrict__ out) {
+  extern __shared__ int4 ring_all[];
+  const uint64_t pol = l2_evict_first_policy();
+  uint32_t num_rows = (uint32_t)num_rows_max;
+  if (d_num_rows && *d_num_rows < num_rows) num_rows = *d_num_rows;
+  const unsigned lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  int4 *ring = ring_all + (size_t)wib * STAGES * kStageChunks;
+  const uint32_t warp = blockIdx.x * kRingWarps + wib;
+  const uint32_t num_warps = gridDim.x * kRingWarps;
+  const uint32_t num_groups = (num_rows + 31) / 32;
+  const uint32_t q = 32u / cpr, rem = 32u % cpr;
+  const bool by_table = (mode == kByNode) && st.cache_table != nullptr;
+  const uint32_t lane_row0 = lane / cpr, lane_col0 = lane - lane_row0 * cpr;
+
+  auto group_rows = [&](uint32_t g) { return (num_rows - g * 32) < 32 ? (num_rows - g * 32) : 32u; };
+  auto route = [&](uint32_t idx, uint32_t rank_in) -> const char * {
+    uint32_t rank = kEmpty;
+    if (mode == kCacheRank) rank = idx;
+    else if (by_table) rank = rank_in;
+    if (rank == kEmpty) return static_cast<const char *>(st.host) + (size_t)idx * st.row_bytes;
+    const uint32_t part = rank % st.num_part;
+    return static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
+  };
+  auto dst_of = [&](uint32_t g, uint32_t rows) -> char * {
+    if (lane >= rows) return nullptr;
+    const size_t drow = dst_idx ? (size_t)dst_idx[g * 32 + lane] : (size_t)g * 32 + lane;
+    return out + drow * st.row_bytes;
+  };
+
+  GroupCursor is{warp, 0, 0, lane_row0, lane_col0}, dr = is;
+  if (warp >= num_groups) return;
+  is.rows = dr.rows = group_rows(warp);
+  // look-ahead registers of the issue side: index of the next group, rank of the current one
+  uint32_t idx_cur = 0, rank_cur = kEmpty, idx_nxt = 0, rank_nxt = kEmpty;
+  {
+    const uint32_t r = warp * 32 + lane;
+    if (r < num_rows) {
+      idx_cur = src_idx[r];
+      if (by_table) rank_cur = __ldg(st.cache_table + idx_cur);
+    }
+    const uint64_t rn = (uint64_t)(warp + num_warps) * 32 + lane;
+    if (rn < num_rows) {
+      idx_nxt = src_idx[rn];
+      if (by_table) rank_nxt = __ldg(st.cache_table + idx_nxt);
+    }
+  }
+  const char *sp = lane < is.rows ? route(idx_cur, rank_cur) : nullptr;
+  char *dp = dst_of(dr.g, dr.rows);
+  bool issue_more = true;
+  uint32_t inflight = 0, slot_i = 0, slot_d = 0;
+
+  while (true) {
+    // ---- issue stages until the ring is full ----
+    while (issue_more && inflight < (uint32_t)STAGES) {
+      const uint32_t total = is.rows * cpr;
+      int4 *stage = ring + (size_t)slot_i * kStageChunks;
+#pragma unroll
+      for (int u = 0; u < kStageChunks / 32; ++u) {
+        const uint32_t f = is.stage * kStageChunks + u * 32 + lane;
+        const unsigned long long s64 =
+            __shfl_sync(0xffffffffu, (unsigned long long)reinterpret_cast<uintptr_t>(sp), is.row & 31);
+        if (f < total) cp_async16(stage + u * 32 + lane, reinterpret_cast<const int4 *>(s64) + is.col, pol);
+        is.row += q;
+        is.col += rem;
+        if (is.col >= cpr) { is.col -= cpr; ++is.row; }
+      }
+      cp_async_commit();
+      ++inflight;
+      slot_i = slot_i + 1 == (uint32_t)STAGES ? 0 : slot_i + 1;
+      if ((++is.stage) * kStageChunks >= total) {  // group finished: move to the next one
+        is.g += num_warps;
+        if (is.g >= num_groups) {
+          issue_more = false;
+        } else {
+          is.stage = 0;
+          is.rows = group_rows(is.g);
+          is.row = lane_row0;
+          is.col = lane_col0;
+          sp = lane < is.rows ? route(idx_nxt, rank_nxt) : nullptr;
+          const uint64_t rn = (uint64_t)(is.g + num_warps) * 32 + lane;  // look-ahead for the group after
+          idx_nxt = 0;
+          rank_nxt = kEmpty;
+          if (rn < num_rows) {
+            idx_nxt = src_idx[rn];
+            if (by_table) rank_nxt = __ldg(st.cache_table + idx_nxt);
+          }
+        }
+      }
+    }
+    if (inflight == 0) break;
+    // ---- drain the oldest stage ----
+    if (inflight == (uint32_t)STAGES) cp_async_wait<STAGES - 1>();
+    else cp_async_wait<0>();
+    __syncwarp();
+    {
+      const uint32_t total = dr.rows * cpr;
+      const int4 *stage = ring + (size_t)slot_d * kStageChunks;
+      int4 v[kStageChunks / 32];
+#pragma unroll
+      for (int u = 0; u < kStageChunks / 32; ++u) v[u] = stage[u * 32 + lane];
+#pragma unroll
+      for (int u = 0; u < kStageChunks / 32; ++u) {
+        const uint32_t f = dr.stage * kStageChunks + u * 32 + lane;
+        const unsigned long long d64 =
+            __shfl_sync(0xffffffffu, (unsigned long long)reinterpret_cast<uintptr_t>(dp), dr.row & 31);
+        if (f < total) st_stream_hint(reinterpret_cast<int4 *>(d64) + dr.col, v[u], pol);
+        dr.row += q;
+        dr.col += rem;
+        if (dr.col >= cpr) { dr.col -= cpr; ++dr.row; }
+      }
+      __syncwarp();  // every lane has read the stage before the issue side overwrites it
+      --inflight;
+      slot_d = slot_d + 1 == (uint32_t)STAGES ? 0 : slot_d + 1;
+      if ((++dr.stage) * kStageChunks >= total) {
+        dr.g += num_warps;
+        if (dr.g < num_groups) {
+          dr.stage = 0;
+          dr.rows = group_rows(dr.g);
+          dr.row = lane_row0;
+          dr.col = lane_col0;
+          dp = dst_of(dr.g, dr.rows);
+        }
+      }
+    }
+  }
+}
+
 bool aligned_to(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
 int pick_vector_width(const xg_feature_store &st, const void *out) {
@@ -205,8 +383,46 @@ int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx,
                                                                                num_rows, d_num_rows, cpr, o, st64)
   static const int variant = [] {
     const char *e = std::getenv("XG_GATHER_VARIANT");
-    return e ? std::atoi(e) : 0;
+    return e ? std::atoi(e) : 2;  // 2 = shared-memory ring (default), 0 / 1 = register-staged <16,4,4> / <16,8,2>
   }();
+  if (vw == 16 && variant >= 2 && stats == nullptr) {
+    // shared-memory ring: XG_GATHER_RING_CTAS CTAs per SM (default 2), XG_GATHER_RING_STAGES x 2 KB per warp
+    // (default 3).  Measured on B200, papers100M-shape batch (profiles/r01d_sweep*.txt): alone 0.91-0.96 ms for
+    // every setting with >= 48 KB per SM in flight (register-staged kernel: 0.92-0.94); with the next batch's
+    // sample phase running beside it 1.42 ms/minibatch at (2 CTAs, 3 stages) vs 1.48 for the register-staged
+    // kernel and 1.56 with the two phases on one stream.
+    static const int ring_ctas = [] {
+      const char *e = std::getenv("XG_GATHER_RING_CTAS");
+      const int v = e ? std::atoi(e) : 2;
+      return v < 1 ? 1 : (v > 4 ? 4 : v);
+    }();
+    static const int ring_stages = [] {
+      const char *e = std::getenv("XG_GATHER_RING_STAGES");
+      return e ? std::atoi(e) : 3;
+    }();
+    const size_t ring_ctas_needed = (groups + kRingWarps - 1) / kRingWarps;
+    const unsigned grid = grid_for(ring_ctas_needed, ring_ctas);
+#define XG_RING(S)                                                                                                \
+  do {                                                                                                            \
+    const size_t smem = (size_t)kRingWarps * S * kStageChunks * sizeof(int4);                                     \
+    static const bool attr_set = cudaFuncSetAttribute(gather_rows_ring_kernel<S>,                                 \
+                                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess; \
+    XG_REQUIRE(attr_set, "cannot reserve shared memory for the ring gather");                                     \
+    gather_rows_ring_kernel<S><<<grid, kRingWarps * 32, smem, s>>>(st, mode, src_idx, dst_idx, num_rows,          \
+                                                                   d_num_rows, cpr, o);                           \
+  } while (0)
+    switch (ring_stages) {
+      case 2: XG_RING(2); break;
+      case 3: XG_RING(3); break;
+      case 4: XG_RING(4); break;
+      case 6: XG_RING(6); break;
+      case 8: XG_RING(8); break;
+      default: XG_RING(3); break;
+    }
+#undef XG_RING
+    XG_LAUNCHED();
+    return XG_OK;
+  }
   switch (vw) {
     case 16:
       // measured on B200 (papers100M-shape batch, 4.9 M x 512 B rows): U=4/4 CTAs 0.925 ms, U=8/2 CTAs 0.920,

@@ -85,7 +85,10 @@ struct xg_batch {
   BatchCounts *h_counts = nullptr;
   uint32_t *h_seeds = nullptr;
   cudaEvent_t done = nullptr;
-  cudaGraphExec_t graph = nullptr;
+  cudaEvent_t tl[3] = {};                 // XG_TIMELINE=1: sample begin / extract begin / extract end (timed)
+  cudaEvent_t sampled = nullptr;          // the sample phase of this batch has been enqueued up to here
+  cudaGraphExec_t graph = nullptr;        // sample phase (whole Task when the sampler runs on one stream)
+  cudaGraphExec_t graph_x = nullptr;      // extract phase (two-stream mode)
   uint64_t key = 0;
   uint32_t num_seeds = 0;
   bool recorded = false;  // `done` has been recorded at least once
@@ -109,14 +112,19 @@ struct xg_sampler {
   uint32_t *dst_global = nullptr, *pos = nullptr;  // per-layer scratch, reused layer after layer
   void *scan_mem = nullptr;
   size_t scan_bytes = 0, scan_tiles_a = 0, scan_tiles_b = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr;    // sample phase: shares the hash table and the per-layer scratch -> strictly ordered
+  cudaStream_t xstream = nullptr;   // extract phase: touches only the batch slot's own buffers (== stream in 1-stream mode)
   bool own_stream = false;
+  bool two_streams = false;
+  bool timeline = false;            // XG_TIMELINE=1: timed events around both phases of every batch
+  cudaEvent_t origin = nullptr;
   bool use_graph = true;
   bool stage_timing = false;
   bool uniform = true;      // KHop0/2/3: fused sample + insert kernel
   ExtWorkspace ext;         // scratch of the with-replacement / weighted samplers
   WeightTables weights;
   uint32_t launches_per_batch = 0;
+  uint32_t launches_phase[2] = {0, 0};
   std::mutex mu;
   std::vector<xg_batch *> slots;
   std::atomic<bool> dirty{false};  // a batch overflowed: unnumbered keys may be left in the table
@@ -155,6 +163,9 @@ int alloc_slot(xg_sampler *s, xg_batch **out) {
   XG_CUDA(cudaHostAlloc(&b->h_counts, sizeof(BatchCounts), cudaHostAllocDefault));
   XG_CUDA(cudaHostAlloc(&b->h_seeds, B * sizeof(uint32_t), cudaHostAllocDefault));
   XG_CUDA(cudaEventCreateWithFlags(&b->done, cudaEventDisableTiming));
+  XG_CUDA(cudaEventCreateWithFlags(&b->sampled, s->timeline ? cudaEventDefault : cudaEventDisableTiming));
+  if (s->timeline)
+    for (auto &e : b->tl) XG_CUDA(cudaEventCreate(&e));
   if (s->stage_timing) {
     b->marks.resize(5 + 3 * L);
     for (auto &e : b->marks) XG_CUDA(cudaEventCreate(&e));
@@ -166,7 +177,11 @@ int alloc_slot(xg_sampler *s, xg_batch **out) {
 void free_slot(xg_batch *b) {
   if (!b) return;
   if (b->graph) cudaGraphExecDestroy(b->graph);
+  if (b->graph_x) cudaGraphExecDestroy(b->graph_x);
   if (b->done) cudaEventDestroy(b->done);
+  if (b->sampled) cudaEventDestroy(b->sampled);
+  for (auto e : b->tl)
+    if (e) cudaEventDestroy(e);
   for (auto e : b->marks) cudaEventDestroy(e);
   cudaFree(b->seeds);
   cudaFree(b->seed_local);
@@ -186,8 +201,12 @@ void free_slot(xg_batch *b) {
   delete b;
 }
 
-// The whole Task, stream-ordered; no host synchronisation, no allocation (capturable).
-int enqueue_batch(xg_sampler *s, xg_batch *b) {
+// The Task in two stream-ordered phases; no host synchronisation, no allocation (capturable).
+//   sample phase  (s->stream):  Reset .. collect_counts: uses the sampler-wide hash table and scratch
+//   extract phase (s->xstream): feature + label gather and the one D2H: reads only slot-owned buffers
+// so the extract phase of batch i (HBM/NVLink-bandwidth bound) runs while batch i+1 is being sampled
+// (latency bound, ~20 % of DRAM bandwidth).
+int enqueue_sample(xg_sampler *s, xg_batch *b) {
   cudaStream_t st = s->stream;
   const int L = (int)s->cfg.num_layer;
   const size_t B = s->cfg.batch_size;
@@ -260,6 +279,18 @@ int enqueue_batch(xg_sampler *s, xg_batch *b) {
   collect_counts_kernel<<<1, 32, 0, st>>>(t, L + 1, b->d_counts);
   XG_LAUNCHED();
   mark();
+  return XG_OK;
+}
+
+int enqueue_extract(xg_sampler *s, xg_batch *b) {
+  cudaStream_t st = s->xstream;
+  const int L = (int)s->cfg.num_layer;
+  const size_t B = s->cfg.batch_size;
+  const uint32_t *d_nseed32 = &b->d_params->num_seeds32;
+  int rc = XG_OK;
+  auto mark = [&]() {
+    if (s->stage_timing && b->num_marks < (int)b->marks.size()) cudaEventRecord(b->marks[b->num_marks++], st);
+  };
   if (s->has_store) {  // DoArch6GetCacheMissIndex + DoArch6GPUCacheFeatureCopy in one launch
     rc = launch_gather(s->store, kByNode, b->input_nodes, nullptr, s->cap_input, &b->d_counts->items[L + 1],
                        b->feat, nullptr, st);
@@ -393,15 +424,31 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
     }
     (void)max_f;
   }
-  if (cfg->stream) {
-    s->stream = as_stream(cfg->stream);
-  } else {
-    XG_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
-    s->own_stream = true;
-  }
   const char *env = std::getenv("XG_NO_GRAPH");
   s->stage_timing = (cfg->flags & XG_SAMPLER_STAGE_TIMING) != 0;
   s->use_graph = !(cfg->flags & (XG_SAMPLER_NO_GRAPH | XG_SAMPLER_STAGE_TIMING)) && !(env && env[0] == '1');
+  const char *one = std::getenv("XG_SINGLE_STREAM");
+  s->two_streams = !s->stage_timing && !(cfg->flags & XG_SAMPLER_SINGLE_STREAM) && !(one && one[0] == '1');
+  if (const char *fg = std::getenv("XG_L2_FETCH")) {  // experiment knob: 32 / 64 / 128-byte L2 fetch granularity
+    cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(fg));
+  }
+  const char *tl = std::getenv("XG_TIMELINE");
+  s->timeline = tl && tl[0] == '1';
+  int prio_low = 0, prio_high = 0;
+  XG_CUDA(cudaDeviceGetStreamPriorityRange(&prio_low, &prio_high));
+  if (cfg->stream) {
+    s->stream = as_stream(cfg->stream);
+  } else {
+    // the sample phase is a chain of short latency-bound kernels: let its CTAs go first
+    XG_CUDA(cudaStreamCreateWithPriority(&s->stream, cudaStreamNonBlocking, prio_high));
+    s->own_stream = true;
+  }
+  if (s->two_streams) XG_CUDA(cudaStreamCreateWithPriority(&s->xstream, cudaStreamNonBlocking, prio_low));
+  else s->xstream = s->stream;
+  if (s->timeline) {
+    XG_CUDA(cudaEventCreate(&s->origin));
+    XG_CUDA(cudaEventRecord(s->origin, s->stream));
+  }
   const uint32_t nslots = cfg->num_slots ? cfg->num_slots : 2;
   for (uint32_t i = 0; i < nslots; ++i) {
     xg_batch *b = nullptr;
@@ -420,13 +467,16 @@ int xg_sampler_destroy(xg_sampler *s) {
   if (!s) return XG_OK;
   DeviceScope scope(s->device);
   if (s->stream) cudaStreamSynchronize(s->stream);
+  if (s->two_streams && s->xstream) cudaStreamSynchronize(s->xstream);
   for (auto *b : s->slots) free_slot(b);
   cudaFree(s->dst_global);
   cudaFree(s->pos);
   cudaFree(s->scan_mem);
   ext_release(s->ext);
   if (s->table) xg_hashtable_destroy(s->table);
+  if (s->origin) cudaEventDestroy(s->origin);
   if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
+  if (s->two_streams && s->xstream) cudaStreamDestroy(s->xstream);
   delete s;
   return XG_OK;
 }
@@ -489,40 +539,57 @@ int xg_sampler_submit(xg_sampler *s, const uint32_t *seeds, size_t num_seeds, in
   if (cudaMemcpyAsync(b->d_params, b->h_params, sizeof(BatchParams), cudaMemcpyHostToDevice, st) != cudaSuccess)
     return fail(XG_ERR_CUDA);
 
-  if (s->use_graph) {
-    if (!b->graph) {  // first use of this slot: record the chain once
+  cudaStream_t xs = s->xstream;
+  // one phase: either replay its graph (captured on first use of the slot) or enqueue it directly
+  auto run_phase = [&](cudaStream_t on, cudaGraphExec_t *exec, int (*enqueue)(xg_sampler *, xg_batch *),
+                       uint32_t *count) -> int {
+    if (!s->use_graph) return enqueue(s, b);
+    if (!*exec) {
       const uint64_t before = g_launches.load();
       cudaGraph_t g = nullptr;
-      if (cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
+      if (cudaStreamBeginCapture(on, cudaStreamCaptureModeThreadLocal) != cudaSuccess) {
         set_error("cudaStreamBeginCapture failed");
-        return fail(XG_ERR_CUDA);
+        return XG_ERR_CUDA;
       }
-      rc = enqueue_batch(s, b);
-      cudaError_t e = cudaStreamEndCapture(st, &g);
-      s->launches_per_batch = (uint32_t)(g_launches.load() - before);
+      int r = enqueue(s, b);
+      cudaError_t e = cudaStreamEndCapture(on, &g);
+      *count = (uint32_t)(g_launches.load() - before);  // kernels recorded into the graph, not launched yet
       g_launches.store(before);
-      if (rc || e != cudaSuccess || !g) {
-        if (!rc) set_error(std::string("graph capture failed: ") + cudaGetErrorString(e));
+      if (r || e != cudaSuccess || !g) {
+        if (!r) set_error(std::string("graph capture failed: ") + cudaGetErrorString(e));
         if (g) cudaGraphDestroy(g);
-        return fail(rc ? rc : XG_ERR_CUDA);
+        return r ? r : XG_ERR_CUDA;
       }
-      e = cudaGraphInstantiate(&b->graph, g, 0);
+      e = cudaGraphInstantiate(exec, g, 0);
       cudaGraphDestroy(g);
       if (e != cudaSuccess) {
         set_error(std::string("cudaGraphInstantiate: ") + cudaGetErrorString(e));
-        return fail(XG_ERR_CUDA);
+        return XG_ERR_CUDA;
       }
     }
-    if (cudaGraphLaunch(b->graph, st) != cudaSuccess) {
+    if (cudaGraphLaunch(*exec, on) != cudaSuccess) {
       set_error(std::string("cudaGraphLaunch: ") + cudaGetErrorString(cudaGetLastError()));
-      return fail(XG_ERR_CUDA);
+      return XG_ERR_CUDA;
     }
-    g_launches.fetch_add(s->launches_per_batch);
-  } else {
-    const uint64_t before = g_launches.load();
-    if ((rc = enqueue_batch(s, b))) return fail(rc);
-    s->launches_per_batch = (uint32_t)(g_launches.load() - before);
+    return XG_OK;
+  };
+  const uint64_t launches_before = g_launches.load();
+  if (s->timeline) cudaEventRecord(b->tl[0], st);
+  if ((rc = run_phase(st, &b->graph, enqueue_sample, &s->launches_phase[0]))) return fail(rc);
+  if (s->two_streams) {  // extract phase of this batch waits for its own sample phase only
+    if (cudaEventRecord(b->sampled, st) != cudaSuccess || cudaStreamWaitEvent(xs, b->sampled, 0) != cudaSuccess)
+      return fail(XG_ERR_CUDA);
   }
+  if (s->timeline) cudaEventRecord(b->tl[1], xs);
+  if ((rc = run_phase(xs, &b->graph_x, enqueue_extract, &s->launches_phase[1]))) return fail(rc);
+  if (s->use_graph) {
+    s->launches_per_batch = s->launches_phase[0] + s->launches_phase[1];
+    g_launches.store(launches_before + s->launches_per_batch);
+  } else {
+    s->launches_per_batch = (uint32_t)(g_launches.load() - launches_before);
+  }
+  st = xs;
+  if (s->timeline) cudaEventRecord(b->tl[2], st);
   if (cudaEventRecord(b->done, st) != cudaSuccess) return fail(XG_ERR_CUDA);
   b->recorded = true;
   *out = b;
@@ -600,7 +667,22 @@ int xg_batch_stage_ms(xg_batch *b, int stage, int layer, float *ms) {
   return XG_OK;
 }
 
+/* XG_TIMELINE=1 only: ms since sampler creation of {sample begin, sample end, extract begin, extract end} */
+int xg_batch_timeline(xg_batch *b, float ms[4]) {
+  XG_REQUIRE(b && b->owner && ms, "NULL argument");
+  xg_sampler *s = b->owner;
+  XG_REQUIRE(s->timeline && s->two_streams, "set XG_TIMELINE=1 (two-stream mode) before creating the sampler");
+  DeviceScope scope(s->device);
+  XG_CUDA(cudaEventSynchronize(b->tl[2]));
+  XG_CUDA(cudaEventElapsedTime(&ms[0], s->origin, b->tl[0]));
+  XG_CUDA(cudaEventElapsedTime(&ms[1], s->origin, b->sampled));
+  XG_CUDA(cudaEventElapsedTime(&ms[2], s->origin, b->tl[1]));
+  XG_CUDA(cudaEventElapsedTime(&ms[3], s->origin, b->tl[2]));
+  return XG_OK;
+}
+
 void *xg_sampler_stream(xg_sampler *s) { return s ? s->stream : nullptr; }
+void *xg_sampler_extract_stream(xg_sampler *s) { return s ? s->xstream : nullptr; }
 uint32_t xg_sampler_launches_per_batch(xg_sampler *s) { return s ? s->launches_per_batch : 0; }
 
 }  // extern "C"

@@ -316,6 +316,12 @@ class Minibatch:
         """per-edge payload (random-walk visit counts), samgraph_torch_get_graph_data"""
         return self._t(self.view.data[l], (self.num_edge[l],), torch.int32) if self.view.data[l] else None
 
+    def timeline(self):
+        """XG_TIMELINE=1: ms since sampler creation of (sample begin, sample end, extract begin, extract end)."""
+        ms = (ctypes.c_float * 4)()
+        check(lib.xg_batch_timeline(self._h, ms))
+        return tuple(ms)
+
     @property
     def input_nodes(self):
         return self._t(self.view.input_nodes, (self.num_input,), torch.int32)
@@ -350,7 +356,7 @@ class MinibatchSampler:
                  feat_dim: int = 0, feat_dtype: torch.dtype = torch.float32, label: torch.Tensor | int | None = None,
                  sample_type: int = kKHop0, seed: int = 0, num_slots: int = 2, max_input_nodes: int = 0,
                  device: int = 0, use_graph: bool = True, stream: torch.cuda.Stream | None = None,
-                 stage_timing: bool = False, random_walk_length: int = 0, num_random_walk: int = 0,
+                 stage_timing: bool = False, single_stream: bool = False, random_walk_length: int = 0, num_random_walk: int = 0,
                  random_walk_restart_prob: float = 0.0, prob_table: torch.Tensor | None = None,
                  alias_table: torch.Tensor | None = None, prob_prefix_table: torch.Tensor | None = None):
         cfg = _clib.XgSamplerConfig()
@@ -360,7 +366,7 @@ class MinibatchSampler:
         cfg.batch_size = batch_size
         cfg.sample_type = sample_type
         cfg.num_slots = num_slots
-        cfg.flags = (0 if use_graph else 1) | (2 if stage_timing else 0)
+        cfg.flags = (0 if use_graph else 1) | (2 if stage_timing else 0) | (4 if single_stream else 0)
         cfg.feat_dim = feat_dim
         cfg.feat_dtype = _DTYPE_CODE[feat_dtype]
         cfg.seed = seed
@@ -413,6 +419,11 @@ class MinibatchSampler:
     @property
     def stream_ptr(self) -> int:
         return int(lib.xg_sampler_stream(self._h) or 0)
+
+    @property
+    def extract_stream(self) -> torch.cuda.Stream:
+        """Stream the extract phase (and therefore the end of every batch) is ordered on."""
+        return torch.cuda.ExternalStream(int(lib.xg_sampler_extract_stream(self._h) or 0), device=self.device)
 
 
 def predict_num_nodes(batch_size: int, fanout) -> int:
