@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-steps", type=int, default=20, help="steps of the per-stage CUDA-event pass")
+    ap.add_argument("--replicate", type=float, default=float(os.environ.get("XG_BENCH_REPLICATE", "0.5")),
+                    help="N > 1 only: fraction of the nodes (hottest first, by degree rank) whose feature rows every GPU "
+                         "keeps in its own HBM; the rest is sharded rank %% P (0 = the reference's pure sharding)")
     return ap.parse_args()
 
 
@@ -268,6 +271,19 @@ def run_reference(args):
     }))
 
 
+def placement_note(args, world, V, row_bytes):
+    if world == 1:
+        return "GGMS: topology + features in 1 GPU's HBM, cache 100%"
+    rep = args.replicate
+    gb = V * row_bytes / 1e9
+    if rep <= 0:
+        return (f"GGMS: topology + features sharded over {world} GPUs (v % P / rank % P), cache 100%, "
+                f"{gb / world:.1f} GB of rows per GPU, peers read over NVLink")
+    return (f"GGMS two-tier: topology sharded over {world} GPUs (v % P); features: hottest {rep:.0%} of nodes by degree rank "
+            f"replicated in every GPU ({gb * rep:.1f} GB), remaining {1 - rep:.0%} sharded rank % P "
+            f"({gb * (1 - rep) / world:.1f} GB per GPU) and read from peers over NVLink; cache 100%")
+
+
 def workload_config(args, V, E, world):
     from xgnn_b200 import dataset as D
     dim, dtype = D.SHAPES[args.shape][2], str(D.SHAPES[args.shape][3]).replace("torch.float", "fp")
@@ -275,8 +291,9 @@ def workload_config(args, V, E, world):
                         f"({V / 1e6:.1f}M nodes, {E / 1e9:.2f}B edges, {dim}-d {dtype}), batch {args.batch}, "
                         f"sample + unique/remap + feature/label extract per minibatch",
             "shape": args.shape, "scale": args.scale, "num_node": V, "num_edge": E, "batch": args.batch,
-            "fanout_from_seeds": FANOUT[::-1], "placement": f"GGMS: topology + features sharded over {world} GPU(s), "
-                                                             "cache 100%",
+            "fanout_from_seeds": FANOUT[::-1],
+            "placement": placement_note(args, world, V, dim * (2 if "16" in dtype else 4)),
+            "replicate": (args.replicate if world > 1 else 0.0),
             "l2": "inputs larger than L2 (store is GBs; fresh seeds every step)"}
 
 
@@ -287,7 +304,7 @@ def exchange_parts(st, dist, torch):
     (init-time only, like DistGraph::_DataIpcShare, dist_graph.cu:274-307), map every peer's shards."""
     from xgnn_b200._clib import check, lib
     P, r = st.world, st.rank
-    names = ["indptr", "indices", "feat_part"]
+    names = ["indptr", "indices", "feat_part"]  # the replica (two-tier store) is private: never exported
     mine, raw = [], {}
     for nm in names:
         t = st.local[nm]
@@ -336,7 +353,7 @@ def run_xgnn(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     V, E, dim, dtype, ncls, frac = D.SHAPES[args.shape]
     t_build = time.perf_counter()
-    st = D.build_store(args.shape, local, rank, world, scale=args.scale)
+    st = D.build_store(args.shape, local, rank, world, scale=args.scale, replicate_pct=args.replicate)
     if world > 1:
         ptrs = exchange_parts(st, dist, torch)
         D.attach(st, ptrs["indptr"], ptrs["indices"], ptrs["feat_part"])
@@ -438,7 +455,8 @@ def stage_pass(R, args):
                                use_graph=False, stage_timing=True)
     L = len(FANOUT)
     acc = {}
-    info = {"edges": [0] * L, "inputs": [0] * L, "rows": 0, "seeds": 0}
+    info = {"edges": [0] * L, "inputs": [0] * L, "rows": 0, "seeds": 0, "src_local": 0, "src_peer": 0, "src_host": 0}
+    stats = torch.zeros(4, dtype=torch.int64, device="cuda")
     n = min(args.stage_steps, args.steps)
     for i in range(args.warmup, args.warmup + n):
         hnd = sm2.submit(R["d_flat"][R["offs"][i]:R["offs"][i + 1]], batch_key=i)
@@ -454,6 +472,11 @@ def stage_pass(R, args):
             info["inputs"][l] += mb.num_dst[l]
         info["rows"] += mb.num_input
         info["seeds"] += mb.num_output
+        if st.store is not None:  # where the rows came from (counted by a separate launch, outside the timed marks)
+            stats.zero_()
+            ops.ExtractGGMS(st.store, mb.input_nodes, st.dim, st.dtype, stats=stats, out=mb.feat)
+            c = stats.cpu().tolist()
+            info["src_local"] += c[0]; info["src_peer"] += c[1]; info["src_host"] += c[2]
         mb.release()
     del sm2
     return {k: v / n for k, v in acc.items()}, {k: ([x / n for x in v] if isinstance(v, list) else v / n)
@@ -482,8 +505,21 @@ def main():
             stages[k]["alg_GBps"] = round(alg[k] / ms / 1e6, 1)
     top = max((k for k in stage_ms if k in alg), key=lambda k: stage_ms[k])
     achieved = alg[top] / stage_ms[top] / 1e6
-    if world > 1:  # multi-GPU feature gather: (P-1)/P of the rows arrive over NVLink
-        roof_note = f"{top}: {(world - 1)}/{world} of gathered rows are NVLink peer loads; HBM peak shown for reference"
+    bound, peak_used, frac = "hbm", peak, achieved / peak
+    if world > 1 and top == "feature":
+        # T_roof = max((R_local + W_all) / BW_hbm, R_peer / BW_nvlink_in); fraction = T_roof / T_measured
+        nvl = 770.0  # GB/s per direction per GPU: the measured peer copy B200_PROFILING.md states (our probe: 822-830)
+        r_local, r_peer = info["src_local"] * row_bytes, info["src_peer"] * row_bytes
+        t_hbm = (r_local + info["rows"] * (row_bytes + 4)) / (peak * 1e6)
+        t_nvl = r_peer / (nvl * 1e6)
+        t_roof = max(t_hbm, t_nvl)
+        frac = t_roof / stage_ms[top]
+        if t_nvl >= t_hbm:
+            bound, peak_used, achieved = "nvlink", nvl, r_peer / stage_ms[top] / 1e6
+        roof_note = (f"feature gather: {info['src_local'] / max(info['rows'], 1):.1%} of rows from local HBM, "
+                     f"{info['src_peer'] / max(info['rows'], 1):.1%} from NVLink peers; roofline time "
+                     f"max(HBM {t_hbm:.3f} ms, NVLink-in {t_nvl:.3f} ms) vs measured {stage_ms[top]:.3f} ms; "
+                     f"peaks: HBM {peak:.0f} GB/s measured copy, NVLink {nvl:.0f} GB/s per direction")
     else:
         roof_note = f"{top}: all rows local HBM"
     traffic = None
@@ -505,8 +541,8 @@ def main():
                 "note": "host seeds -> xg_sampler_submit (H2D inside) -> xg_batch_wait (D2H counts); two batches in flight"},
         "gpu_launches": int(R["launches"]),
         "clocks": R["clk"],
-        "roofline": {"bound": "hbm", "kernel": top, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src, "note": roof_note,
+        "roofline": {"bound": bound, "kernel": top, "achieved": round(achieved, 1), "peak": peak_used, "unit": "GB/s",
+                     "frac": round(frac, 4), "traffic": traffic if world == 1 else None, "peak_source": peak_src, "note": roof_note,
                      "alg_bytes_per_launch": int(alg[top]), "launch_ms": round(stage_ms[top], 4)},
         "stages": stages,
         "epoch": {"steps_per_epoch": steps_per_epoch, "sample_extract_time_s": steps_per_epoch * R["ms"] / args.steps / 1e3,

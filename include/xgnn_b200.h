@@ -78,6 +78,11 @@ typedef struct xg_graph {
  *   cache_table == NULL : every row comes from `host` (which may just as well be device memory).
  *   otherwise r = cache_table[node]; r == XG_EMPTY_KEY -> `host` row `node`;
  *             else part r % num_part, row r / num_part.
+ * B200 extension (num_replicated > 0): the hottest cache ranks r < num_replicated are REPLICATED in every GPU's
+ * own HBM (`replica`, row r) and only the remaining ranks r' = r - num_replicated are partitioned
+ * (part r' % num_part, row r' / num_part).  In the reference's vocabulary this is a cache split into a
+ * clique_size = 1 tier and a clique_size = P tier (run_config `clique_size`, cuda/dist_graph.cu:392-480);
+ * num_replicated = 0 is exactly the reference's DeviceDistFeature routing (cuda/dist_graph.h:203-207).
  */
 typedef struct xg_feature_store {
   const void *part[XG_MAX_PARTS];
@@ -86,6 +91,9 @@ typedef struct xg_feature_store {
   uint32_t num_part;
   uint32_t local_part_mask; /* bit p set: part p is in this GPU's HBM (statistics only) */
   uint64_t row_bytes;       /* dim * sizeof(dtype) */
+  const void *replica;      /* rows of cache ranks [0, num_replicated) in THIS GPU's HBM, or NULL */
+  uint32_t num_replicated;
+  uint32_t reserved;
 } xg_feature_store;
 
 /* ------------------------------------------------------------------------------------------------

@@ -206,6 +206,36 @@ def extract_ggms(feat, nodes, table, parts):
     return out
 
 
+def hybrid_placement(feat, rank_nodes, num_cached, num_replicated, num_part):
+    """Two-tier GGMS placement (B200 extension, include/xgnn_b200.h xg_feature_store): cache ranks
+    [0, num_replicated) form the replica every GPU holds; rank r >= num_replicated goes to part
+    (r - num_replicated) % P, row (r - num_replicated) / P, i.e. DeviceDistFeature's rule
+    (cuda/dist_graph.h:203-207, cuda/dist_graph.cu:493-505) applied to the remaining ranks."""
+    ranked = u32(rank_nodes)[:num_cached]
+    replica = np.ascontiguousarray(feat[ranked[:num_replicated]])
+    rest = ranked[num_replicated:]
+    parts = [np.ascontiguousarray(feat[rest[p::num_part]]) for p in range(num_part)]
+    return replica, parts
+
+
+def extract_hybrid(feat, nodes, table, replica, parts):
+    """Row-by-row routing oracle of the two-tier store (numpy restatement of route_row in csrc/extract.cu,
+    which follows DeviceDistFeature::Get, cuda/dist_graph.h:203-207, after removing the replicated ranks)."""
+    nodes = u32(nodes)
+    out = np.empty((len(nodes),) + feat.shape[1:], feat.dtype)
+    P, nrep = len(parts), len(replica)
+    for i, v in enumerate(nodes):
+        r = int(table[v])
+        if r == 0xFFFFFFFF:
+            out[i] = feat[v]
+        elif r < nrep:
+            out[i] = replica[r]
+        else:
+            r -= nrep
+            out[i] = parts[r % P][r // P]
+    return out
+
+
 _sig(orc, "orc_minibatch", c_size_t, u32p, u32p, u32p, c_size_t, POINTER(c_size_t), c_int, c_uint64,
      POINTER(c_void_p), POINTER(c_void_p), POINTER(c_size_t), u32p, c_size_t)
 

@@ -294,3 +294,34 @@ def test_extract_ggms_vs_oracle(ops, P, pct):
     ops.CombineCacheData(out2, store, gcs, gcd)
     assert torch.equal(out, out2)
     torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("P", [1, 2, 8])
+@pytest.mark.parametrize("pct,rep", [(1.0, 0.25), (0.6, 0.6), (0.5, 0.1), (1.0, 1.0)])
+def test_extract_two_tier_store_vs_oracle(ops, P, pct, rep):
+    """Hot ranks replicated, the rest partitioned, misses from pinned host: same rows as CPUExtract."""
+    V, dim = 30000, 100
+    feat = synth.make_features(V, dim)
+    indptr, _ = synth.make_graph(V, 200000, seed=5)
+    rank = synth.degree_rank(indptr)
+    ncached, nrep = int(V * pct), int(V * rep)
+    table = O.build_cache_table(rank, ncached, V)
+    replica, parts = O.hybrid_placement(feat, rank, ncached, nrep, P)
+    d_parts = [dev(p) if len(p) else torch.zeros((1, dim), device="cuda") for p in parts]
+    d_rep = dev(replica) if nrep else None
+    h_feat = torch.from_numpy(feat).pin_memory()
+    store = ops.make_feature_store(dim * 4, h_feat, dev(table), d_parts, local_parts=(0,), replica=d_rep,
+                                   num_replicated=nrep)
+    nodes = np.random.default_rng(11).integers(0, V, size=20011).astype(np.uint32)
+    stats = torch.zeros(4, dtype=torch.int64, device="cuda")
+    out = ops.ExtractGGMS(store, dev(nodes), dim, torch.float32, stats=stats)   # register-staged kernel (stats)
+    out_ring = ops.ExtractGGMS(store, dev(nodes), dim, torch.float32)            # shared-memory ring kernel
+    want = O.extract_hybrid(feat, nodes, table, replica, parts)
+    assert np.array_equal(want.view(np.uint32), O.extract(feat, nodes).view(np.uint32))  # placement never changes rows
+    assert np.array_equal(host(out).view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(host(out_ring).view(np.uint32), want.view(np.uint32))
+    r = table[nodes]
+    hit = r != 0xFFFFFFFF
+    local = hit & ((r < nrep) | (((r.astype(np.int64) - nrep) % P) == 0))
+    st = stats.cpu().numpy()
+    assert st[2] == (~hit).sum() and st[0] == local.sum() and st[1] == (hit & ~local).sum()

@@ -166,3 +166,22 @@ def test_partitioned_features_reassemble(P):
     assert np.array_equal(nodes[md], ms) and np.all(table[ms] == O.EMPTY)
     assert np.array_equal(table[nodes[cd]], cs)
     assert np.all(np.diff(md.astype(np.int64)) > 0) and np.all(np.diff(cd.astype(np.int64)) > 0)
+
+
+def test_two_tier_placement_oracle_reads_the_same_rows():
+    """The replicated + partitioned placement (B200 extension) must never change WHICH row a node resolves to."""
+    import synth
+    V, dim = 5000, 12
+    feat = synth.make_features(V, dim)
+    indptr, _ = synth.make_graph(V, 40000, seed=9)
+    rank = synth.degree_rank(indptr)
+    nodes = np.random.default_rng(3).integers(0, V, size=4001).astype(np.uint32)
+    for ncached, nrep, P in [(5000, 0, 4), (5000, 1250, 8), (3000, 3000, 2), (2000, 100, 1), (0, 0, 3)]:
+        table = O.build_cache_table(rank, ncached, V)
+        replica, parts = O.hybrid_placement(feat, rank, ncached, nrep, P)
+        assert len(replica) == nrep and sum(len(p) for p in parts) == ncached - nrep
+        got = O.extract_hybrid(feat, nodes, table, replica, parts)
+        assert np.array_equal(got.view(np.uint32), O.extract(feat, nodes).view(np.uint32))
+        if nrep == 0 and ncached:  # degenerates to the reference's single-tier routing
+            ref_parts = [O.partition_features(feat, rank, ncached, p, P) for p in range(P)]
+            assert all(np.array_equal(a, b) for a, b in zip(parts, ref_parts))

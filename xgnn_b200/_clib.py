@@ -36,6 +36,9 @@ class XgFeatureStore(Structure):
         ("num_part", c_uint32),
         ("local_part_mask", c_uint32),
         ("row_bytes", c_uint64),
+        ("replica", c_void_p),
+        ("num_replicated", c_uint32),
+        ("reserved", c_uint32),
     ]
 
 

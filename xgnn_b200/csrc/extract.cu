@@ -75,6 +75,11 @@ __device__ __forceinline__ const char *route_row(const xg_feature_store &st, int
     *klass = 2;  // host (or the flat table when nothing is cached)
     return static_cast<const char *>(st.host) + (size_t)idx * st.row_bytes;
   }
+  if (rank < st.num_replicated) {
+    *klass = 0;
+    return static_cast<const char *>(st.replica) + (size_t)rank * st.row_bytes;
+  }
+  rank -= st.num_replicated;
   const uint32_t part = rank % st.num_part;
   *klass = ((st.local_part_mask >> part) & 1u) ? 0 : 1;
   return static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
@@ -138,7 +143,11 @@ gather_rows_kernel(const xg_feature_store st, int mode, const uint32_t *__restri
       else if (by_table) rank = rank_cur;
       if (rank == kEmpty) {
         sp = static_cast<const char *>(st.host) + (size_t)idx_cur * st.row_bytes;
+      } else if (rank < st.num_replicated) {
+        klass = 0;
+        sp = static_cast<const char *>(st.replica) + (size_t)rank * st.row_bytes;
       } else {
+        rank -= st.num_replicated;
         const uint32_t part = rank % st.num_part;
         klass = ((st.local_part_mask >> part) & 1u) ? 0 : 1;
         sp = static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
@@ -240,6 +249,8 @@ gather_rows_ring_kernel(const xg_feature_store st, int mode, const uint32_t *__r
     if (mode == kCacheRank) rank = idx;
     else if (by_table) rank = rank_in;
     if (rank == kEmpty) return static_cast<const char *>(st.host) + (size_t)idx * st.row_bytes;
+    if (rank < st.num_replicated) return static_cast<const char *>(st.replica) + (size_t)rank * st.row_bytes;
+    rank -= st.num_replicated;
     const uint32_t part = rank % st.num_part;
     return static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
   };
@@ -353,6 +364,7 @@ int pick_vector_width(const xg_feature_store &st, const void *out) {
   for (int vw = 16; vw > 1; vw >>= 1) {
     bool ok = (st.row_bytes % vw == 0) && aligned_to(out, vw) && (st.host == nullptr || aligned_to(st.host, vw));
     for (uint32_t p = 0; ok && p < st.num_part; ++p) ok = st.part[p] == nullptr || aligned_to(st.part[p], vw);
+    if (ok && st.num_replicated) ok = aligned_to(st.replica, vw);
     if (ok) return vw;
   }
   return 1;
@@ -367,7 +379,8 @@ int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx,
   XG_REQUIRE(out != nullptr && src_idx != nullptr, "NULL buffer");
   XG_REQUIRE(st.num_part <= XG_MAX_PARTS, "too many partitions");
   XG_REQUIRE(num_rows < 0xFFF00000ull, "too many rows for one launch");
-  XG_REQUIRE(mode != kCacheRank || st.num_part > 0, "cache-rank gather needs a partitioned cache");
+  XG_REQUIRE(mode != kCacheRank || st.num_part > 0 || st.num_replicated > 0, "cache-rank gather needs a cache");
+  XG_REQUIRE(st.num_replicated == 0 || st.replica != nullptr, "num_replicated > 0 but replica is NULL");
   XG_REQUIRE(mode == kCacheRank || st.host != nullptr || st.cache_table != nullptr, "no source table");
   const int vw = pick_vector_width(st, out);
   const uint64_t cpr64 = st.row_bytes / vw;

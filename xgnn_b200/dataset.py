@@ -93,18 +93,22 @@ class GGMSStore:
         return self.dim * torch.empty((), dtype=self.dtype).element_size()
 
 
-def cache_rank_nodes(num_node: int, num_cached: int) -> np.ndarray:
+def cache_rank_nodes(num_node: int, num_cached: int, num_replicated: int = 0) -> np.ndarray:
     """The cached set in cache-rank order: first `num_cached` entries of the degree ranking (for the
     synthetic shapes degree is non-increasing in the id, so the stable ranking is the identity),
     shuffled as GPUCacheManager does (std::shuffle with mt19937(num_cached),
     cuda_cache_manager_host.cc:162-171) so that rank r -> part r % P is load balanced."""
     nodes = np.arange(num_cached, dtype=np.uint32)
-    check(lib.xg_shuffle_cache_ranks(nodes.ctypes.data, num_cached))
+    # two-tier store: the replicated tier keeps the policy order (it is the HOTTEST prefix and needs no
+    # balancing); only the partitioned remainder is shuffled, by the same rule applied to what is left
+    rest = nodes[num_replicated:]
+    if len(rest):
+        check(lib.xg_shuffle_cache_ranks(rest.ctypes.data, len(rest)))
     return nodes
 
 
 def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale: int = 1, cache_pct: float = 1.0,
-                with_features: bool = True, seed: int = SYNTH_SEED) -> GGMSStore:
+                replicate_pct: float = 0.0, with_features: bool = True, seed: int = SYNTH_SEED) -> GGMSStore:
     """Generate THIS rank's shards (topology part `rank`, feature part `rank`) of the named shape,
     scaled down by `scale`. Peer parts are attached afterwards (attach_peers) from IPC handles."""
     V, E, dim, dtype, num_class, train_frac = SHAPES[shape]
@@ -121,13 +125,19 @@ def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale
         st.label = (torch.arange(V, dtype=torch.int64, device=dev) % num_class)
         if with_features:
             n_cached = int(V * cache_pct)
-            ranks = cache_rank_nodes(V, n_cached)
+            n_rep = min(n_cached, int(V * replicate_pct)) if P > 1 else 0
+            ranks = cache_rank_nodes(V, n_cached, n_rep)
             table = np.full(V, 0xFFFFFFFF, np.uint32)
             table[ranks] = np.arange(n_cached, dtype=np.uint32)
             st.local["cache_table"] = torch.from_numpy(table.view(np.int32)).to(dev)
-            mine = torch.from_numpy(np.ascontiguousarray(ranks[rank::P]).view(np.int32)).to(dev)
-            st.local["feat_part"] = gen_features(mine.numel(), dim, dtype, dev, row_ids=mine)
+            mine = torch.from_numpy(np.ascontiguousarray(ranks[n_rep:][rank::P]).view(np.int32)).to(dev)
+            st.local["feat_part"] = gen_features(max(mine.numel(), 1), dim, dtype, dev, row_ids=mine if mine.numel() else None)
             st.local["num_cached"] = n_cached
+            st.local["num_replicated"] = n_rep
+            if n_rep:  # ranks [0, n_rep) are nodes 0..n_rep-1 in policy order: every GPU generates its own copy
+                hot = torch.from_numpy(np.ascontiguousarray(ranks[:n_rep]).view(np.int32)).to(dev)
+                st.local["replica"] = gen_features(n_rep, dim, dtype, dev, row_ids=hot)
+                del hot
             del mine
         torch.cuda.synchronize()
     st.train = train_set(V, max(1, int(V * train_frac)))
@@ -146,5 +156,6 @@ def attach(st: GGMSStore, part_indptr=None, part_indices=None, feat_parts=None, 
                               num_node=st.num_node, host_indptr=None, host_indices=None)
     if st.local.get("cache_table") is not None:
         st.store = ops.make_feature_store(st.row_bytes, host_feat, st.local["cache_table"], parts=feat_parts,
-                                          local_parts=(st.rank,))
+                                          local_parts=(st.rank,), replica=st.local.get("replica"),
+                                          num_replicated=st.local.get("num_replicated", 0))
     return st

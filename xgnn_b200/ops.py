@@ -208,7 +208,7 @@ def GPUExtract(src: torch.Tensor | int, index: torch.Tensor, dim: int | None = N
 
 
 def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_table: torch.Tensor | None = None,
-                       parts=None, local_parts=()) -> XgFeatureStore:
+                       parts=None, local_parts=(), replica=None, num_replicated: int = 0) -> XgFeatureStore:
     """DeviceDistFeature + cache table + host table in one handle (cuda/dist_graph.h:182-213)."""
     st = XgFeatureStore()
 
@@ -227,7 +227,9 @@ def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_ta
     for i in local_parts:
         mask |= 1 << i
     st.local_part_mask = mask
-    st._keep = [host, cache_table, parts]  # raw pointers inside: keep the tensors alive
+    st.replica = p(replica) if num_replicated else None
+    st.num_replicated = num_replicated if replica is not None else 0
+    st._keep = [host, cache_table, parts, replica]  # raw pointers inside: keep the tensors alive
     return st
 
 
