@@ -61,6 +61,30 @@ __device__ __forceinline__ uint32_t table_insert(const TableView &t, uint32_t ke
   return kEmpty;
 }
 
+// The same insert split in two so that a thread can have several first probes in flight before it
+// resolves any of them (sample_uniform_kernel pipelines 4 edges per lane this way):
+//   begin : home slot + the (volatile) load of its key     finish: CAS / linear probing from there
+__device__ __forceinline__ uint32_t table_insert_begin(const TableView &t, uint32_t key, uint32_t *k_out) {
+  const uint32_t p = __umulhi(table_hash(key), t.cap);
+  *k_out = *reinterpret_cast<volatile uint32_t *>(&t.slots[p].x);
+  return p;
+}
+__device__ __forceinline__ uint32_t table_insert_finish(const TableView &t, uint32_t key, uint32_t tagged_pos,
+                                                        uint32_t p, uint32_t k) {
+  for (uint32_t probes = 0; probes < t.cap; ++probes) {
+    uint32_t *kp = &t.slots[p].x;
+    if (probes) k = *reinterpret_cast<volatile uint32_t *>(kp);
+    if (k == kEmpty) k = atomicCAS(kp, kEmpty, key);
+    if (k == kEmpty || k == key) {
+      atomicMin(&t.slots[p].y, tagged_pos);
+      return p;
+    }
+    p = (p + 1 == t.cap) ? 0u : p + 1;
+  }
+  *t.overflow = 1;
+  return kEmpty;
+}
+
 // SearchO2N: slot position of `key`, kEmpty when absent.
 __device__ __forceinline__ uint32_t table_find(const TableView &t, uint32_t key) {
   uint32_t p = __umulhi(table_hash(key), t.cap);

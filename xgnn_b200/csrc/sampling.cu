@@ -25,7 +25,7 @@ namespace xg {
 
 namespace {
 
-template <int G, int VPL, bool FUSED>
+template <int G, int VPL, bool FUSED, bool PIPE>
 __global__ void __launch_bounds__(kSampleBlock)
 sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint32_t num_input_max,
                       const uint32_t *__restrict__ d_num_input, uint32_t fanout,
@@ -93,69 +93,128 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
     const uint64_t tile_base = s_tile_base;
 
     // ---------------- phase B: G lanes per node ---------------------------------------------
-    for (unsigned j = grp; j < kSampleTile; j += kGroups) {
-      const uint32_t ndeg = s_deg[j];
-      const uint32_t *nedges = s_edges[j];
-      const uint64_t obase = tile_base + s_off[j];
-      const uint32_t src = s_src[j];
-      const bool big = ndeg > fanout;
-
-      uint32_t sel[VPL];  // chosen positions (big) for slot k*G + gl
-      if (__any_sync(0xffffffffu, big)) {
-        // Floyd: for slot s = 0..fanout-1, J = deg - fanout + s, t ~ U[0, J]; take t unless already
-        // taken, else take J.  Draws are made lane-parallel up front, conflicts resolved in order.
-        uint32_t draw[VPL];
-        {
-          const uint32_t node_pos = tile * kSampleTile + j;
-          const uint4 r = Philox::rand4(rng_key, make_uint4(node_pos, gl, salt, 0u));
-          const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
-          const uint32_t j0 = big ? (ndeg - fanout) : 0u;
+    if constexpr (VPL == 1 && PIPE) {
+      // fanout <= G: a lane owns at most ONE edge of a node (slot gl).  The tile's nodes are walked kPipe at a
+      // time in three sweeps - positions + neighbour loads, stores + first hash probes, probe resolution - so
+      // every lane has kPipe independent DRAM loads and then kPipe independent L2 probes in flight instead of
+      // one dependent load -> probe -> CAS chain per node (that chain, 8-16 times per tile, was 70 % of the
+      // kernel: ncu r01b long-scoreboard stalls).  Same Philox counters and draws as before: outputs unchanged.
+      // Used for layers of at most one wave of tiles (seed-side layers: latency bound, 0.063 -> 0.046 ms and
+      // 0.088 -> 0.079 ms on B200); the big input-side layer is bound by random-sector DRAM throughput, where the
+      // extra registers (43 vs 32) only cost occupancy (0.26 -> 0.31 ms), so it keeps the plain loop.
+      constexpr int kPipe = 4;
+      static_assert((kSampleTile / kGroups) % kPipe == 0, "tile iterations must be a multiple of the pipeline depth");
+      for (unsigned j0 = grp; j0 < kSampleTile; j0 += kGroups * kPipe) {
+        uint32_t nb[kPipe], slot[kPipe], key0[kPipe];
+        bool live[kPipe];
 #pragma unroll
-          for (int k = 0; k < VPL; ++k) {
-            uint32_t rk = rr[k & 3];
-            if (VPL > 4 && k >= 4) {  // more than four slots per lane: extra Philox blocks
-              const uint4 r2 = Philox::rand4(rng_key, make_uint4(node_pos, gl, salt, (uint32_t)(k >> 2)));
-              const uint32_t rr2[4] = {r2.x, r2.y, r2.z, r2.w};
-              rk = rr2[k & 3];
+        for (int q = 0; q < kPipe; ++q) {  // sweep 1: choose the position, issue the neighbour load
+          const unsigned j = j0 + q * kGroups;
+          const uint32_t ndeg = s_deg[j];
+          const uint32_t *nedges = s_edges[j];
+          const bool big = ndeg > fanout;
+          uint32_t sel = gl;
+          if (__any_sync(0xffffffffu, big)) {
+            const uint32_t node_pos = tile * kSampleTile + j;
+            const uint4 r = Philox::rand4(rng_key, make_uint4(node_pos, gl, salt, 0u));
+            const uint32_t jbase = big ? (ndeg - fanout) : 0u;
+            const uint32_t draw = bounded(r.x, jbase + gl + 1u);
+            uint32_t mine_sel = kEmpty;
+            for (unsigned jl = 0; jl < (unsigned)G; ++jl) {
+              if (jl >= fanout) break;  // uniform across the warp
+              const uint32_t t = __shfl_sync(0xffffffffu, draw, jl, G);
+              const unsigned hits = (__ballot_sync(0xffffffffu, mine_sel == t) >> grp_shift) & kGroupMask;
+              if (gl == jl) mine_sel = hits ? (ndeg - fanout + jl) : t;
             }
-            draw[k] = bounded(rk, j0 + (uint32_t)(k * G) + gl + 1u);
-            sel[k] = kEmpty;
+            if (big) sel = mine_sel;
           }
+          live[q] = gl < (big ? fanout : ndeg);
+          nb[q] = live[q] ? nedges[sel] : 0u;
         }
 #pragma unroll
-        for (int k = 0; k < VPL; ++k) {
-          for (unsigned jl = 0; jl < (unsigned)G; ++jl) {
-            const uint32_t s = (uint32_t)k * G + jl;
-            if (s >= fanout) break;  // uniform across the warp
-            const uint32_t t = __shfl_sync(0xffffffffu, draw[k], jl, G);
-            bool mine = false;
+        for (int q = 0; q < kPipe; ++q) {  // sweep 2: write the edge, start the hash insert
+          if (!live[q]) continue;
+          const unsigned j = j0 + q * kGroups;
+          const uint64_t e = tile_base + s_off[j] + gl;
+          out_dst[e] = nb[q];
+          out_src[e] = s_src[j];
+          if (FUSED) slot[q] = table_insert_begin(fusion.table, nb[q], &key0[q]);
+        }
+        if (FUSED) {
 #pragma unroll
-            for (int kk = 0; kk <= k; ++kk) mine |= (sel[kk] == t);  // unset slots hold kEmpty != t
-            const unsigned hits = (__ballot_sync(0xffffffffu, mine) >> grp_shift) & kGroupMask;
-            if (gl == jl) sel[k] = hits ? (ndeg - fanout + s) : t;
+          for (int q = 0; q < kPipe; ++q) {  // sweep 3: resolve the probes
+            if (!live[q]) continue;
+            const unsigned j = j0 + q * kGroups;
+            const uint64_t e = tile_base + s_off[j] + gl;
+            fusion.pos_out[e] = table_insert_finish(fusion.table, nb[q], kPosTag | (uint32_t)e, slot[q], key0[q]);
           }
         }
       }
+    } else {
+      for (unsigned j = grp; j < kSampleTile; j += kGroups) {
+        const uint32_t ndeg = s_deg[j];
+        const uint32_t *nedges = s_edges[j];
+        const uint64_t obase = tile_base + s_off[j];
+        const uint32_t src = s_src[j];
+        const bool big = ndeg > fanout;
 
-      if (big) {
-#pragma unroll
-        for (int k = 0; k < VPL; ++k) {
-          const uint32_t s = (uint32_t)k * G + gl;
-          if (s < fanout) {
-            const uint32_t nbr = nedges[sel[k]];
+        uint32_t sel[VPL];  // chosen positions (big) for slot k*G + gl
+        if (__any_sync(0xffffffffu, big)) {
+          // Floyd: for slot s = 0..fanout-1, J = deg - fanout + s, t ~ U[0, J]; take t unless already
+          // taken, else take J.  Draws are made lane-parallel up front, conflicts resolved in order.
+          uint32_t draw[VPL];
+          {
+            const uint32_t node_pos = tile * kSampleTile + j;
+            const uint4 r = Philox::rand4(rng_key, make_uint4(node_pos, gl, salt, 0u));
+            const uint32_t rr[4] = {r.x, r.y, r.z, r.w};
+            const uint32_t j0 = big ? (ndeg - fanout) : 0u;
+  #pragma unroll
+            for (int k = 0; k < VPL; ++k) {
+              uint32_t rk = rr[k & 3];
+              if (VPL > 4 && k >= 4) {  // more than four slots per lane: extra Philox blocks
+                const uint4 r2 = Philox::rand4(rng_key, make_uint4(node_pos, gl, salt, (uint32_t)(k >> 2)));
+                const uint32_t rr2[4] = {r2.x, r2.y, r2.z, r2.w};
+                rk = rr2[k & 3];
+              }
+              draw[k] = bounded(rk, j0 + (uint32_t)(k * G) + gl + 1u);
+              sel[k] = kEmpty;
+            }
+          }
+  #pragma unroll
+          for (int k = 0; k < VPL; ++k) {
+            for (unsigned jl = 0; jl < (unsigned)G; ++jl) {
+              const uint32_t s = (uint32_t)k * G + jl;
+              if (s >= fanout) break;  // uniform across the warp
+              const uint32_t t = __shfl_sync(0xffffffffu, draw[k], jl, G);
+              bool mine = false;
+  #pragma unroll
+              for (int kk = 0; kk <= k; ++kk) mine |= (sel[kk] == t);  // unset slots hold kEmpty != t
+              const unsigned hits = (__ballot_sync(0xffffffffu, mine) >> grp_shift) & kGroupMask;
+              if (gl == jl) sel[k] = hits ? (ndeg - fanout + s) : t;
+            }
+          }
+        }
+
+        if (big) {
+  #pragma unroll
+          for (int k = 0; k < VPL; ++k) {
+            const uint32_t s = (uint32_t)k * G + gl;
+            if (s < fanout) {
+              const uint32_t nbr = nedges[sel[k]];
+              const uint64_t e = obase + s;
+              out_dst[e] = nbr;
+              out_src[e] = src;
+              if (FUSED) fusion.pos_out[e] = table_insert(fusion.table, nbr, kPosTag | (uint32_t)e);
+            }
+          }
+        } else {
+          for (uint32_t s = gl; s < ndeg; s += G) {
+            const uint32_t nbr = nedges[s];
             const uint64_t e = obase + s;
             out_dst[e] = nbr;
             out_src[e] = src;
             if (FUSED) fusion.pos_out[e] = table_insert(fusion.table, nbr, kPosTag | (uint32_t)e);
           }
-        }
-      } else {
-        for (uint32_t s = gl; s < ndeg; s += G) {
-          const uint32_t nbr = nedges[s];
-          const uint64_t e = obase + s;
-          out_dst[e] = nbr;
-          out_src[e] = src;
-          if (FUSED) fusion.pos_out[e] = table_insert(fusion.table, nbr, kPosTag | (uint32_t)e);
         }
       }
     }
@@ -170,15 +229,19 @@ int launch_variant(const xg_graph &g, const uint32_t *d_input, size_t num_input_
                    const SampleFusion &fusion, const ScanSpace &scan, cudaStream_t s) {
   const size_t tiles = (num_input_max + kSampleTile - 1) / kSampleTile;
   const unsigned grid = grid_for(tiles, 6);
+  const bool pipe = VPL == 1 && tiles <= (size_t)kNumSM * 6;
+#define XG_LAUNCH_SAMPLE(F, P)                                                                              \
+  sample_uniform_kernel<G, VPL, F, P><<<grid, kSampleBlock, 0, s>>>(                                        \
+      g, d_input, (uint32_t)num_input_max, d_num_input, (uint32_t)fanout, d_out_src, d_out_dst, d_num_out, \
+      key, d_key, salt, fusion, scan.ticket, scan.state)
   if (fusion.enabled) {
-    sample_uniform_kernel<G, VPL, true><<<grid, kSampleBlock, 0, s>>>(
-        g, d_input, (uint32_t)num_input_max, d_num_input, (uint32_t)fanout, d_out_src, d_out_dst,
-        d_num_out, key, d_key, salt, fusion, scan.ticket, scan.state);
+    if (pipe) XG_LAUNCH_SAMPLE(true, true);
+    else XG_LAUNCH_SAMPLE(true, false);
   } else {
-    sample_uniform_kernel<G, VPL, false><<<grid, kSampleBlock, 0, s>>>(
-        g, d_input, (uint32_t)num_input_max, d_num_input, (uint32_t)fanout, d_out_src, d_out_dst,
-        d_num_out, key, d_key, salt, fusion, scan.ticket, scan.state);
+    if (pipe) XG_LAUNCH_SAMPLE(false, true);
+    else XG_LAUNCH_SAMPLE(false, false);
   }
+#undef XG_LAUNCH_SAMPLE
   XG_LAUNCHED();
   return XG_OK;
 }
