@@ -107,3 +107,13 @@ def test_arch6_fork_per_worker_ggms_over_ipc(dataset, sample_type, workers):
     processes through CUDA IPC (both workers may share one GPU on a single-GPU box)"""
     import torch
     _drive("arch6", dataset, sample_type, workers, env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count()))})
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sample_type,workers,rep", [(0, 2, 0.2), (7, 3, 0.5)])
+def test_arch6_two_tier_feature_store(dataset, sample_type, workers, rep):
+    """Same arch6 flow with the hot tier replicated per worker (`ggms_replicate_percentage`, here through its
+    environment twin): every batch's features must still equal CPUExtract's rows bit for bit."""
+    import torch
+    _drive("arch6", dataset, sample_type, workers,
+           env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "SAMGRAPH_GGMS_REPLICATE": str(rep)})

@@ -110,6 +110,7 @@ struct RunConfig {
   int run_arch = 0, sample_type = 0, cache_policy = 0;
   size_t batch_size = 0, num_epoch = 0, num_layer = 0;
   double cache_percentage = 0.0;
+  double replicate_percentage = 0.0;  // `ggms_replicate_percentage`: hot tier replicated per GPU (0 = reference layout)
   std::vector<size_t> fanout;
   size_t random_walk_length = 0, num_random_walk = 0, num_neighbor = 0;
   double random_walk_restart_prob = 0.0;
@@ -551,7 +552,12 @@ void build_feature_store(Engine &e) {
   const bool parted = cfg.run_arch == kArch6 && cfg.part_cache && e.shared != nullptr;
   const uint32_t P = parted ? (uint32_t)e.shared->num_worker : 1u;
   std::vector<uint32_t> ranks(ds.ranking, ds.ranking + n_cached);
-  if (parted) SAM_XG(xg_shuffle_cache_ranks(ranks.data(), n_cached));  // cuda_cache_manager_host.cc:162-171
+  // two-tier store (B200 extension, config key `ggms_replicate_percentage`, default 0 = the reference layout): the
+  // hottest ranks keep the policy order and are replicated per GPU; only the sharded remainder is shuffled
+  size_t n_rep = parted ? (size_t)(V * cfg.replicate_percentage) : 0;
+  if (n_rep > n_cached) n_rep = n_cached;
+  if (parted && n_cached > n_rep)
+    SAM_XG(xg_shuffle_cache_ranks(ranks.data() + n_rep, n_cached - n_rep));  // cuda_cache_manager_host.cc:162-171
   {
     std::vector<uint32_t> table(V, XG_EMPTY_KEY);
     for (size_t r = 0; r < n_cached; ++r) table[ranks[r]] = (uint32_t)r;
@@ -559,23 +565,31 @@ void build_feature_store(Engine &e) {
   }
   const void *h_feat = pin_host(ds.feat, V * row_bytes);
   e.store.num_part = P;
+  auto gather_rows_to_device = [&](const uint32_t *ids, size_t n) -> void * {
+    // CPUExtract + H2D in the reference; here the GPU gathers the rows straight out of the host mapping
+    void *d_rows = dev_alloc(e, std::max<size_t>(n * row_bytes, 16));
+    if (n) {
+      uint32_t *d_ids = nullptr;
+      SAM_CUDA(cudaMalloc(&d_ids, n * sizeof(uint32_t)));
+      SAM_CUDA(cudaMemcpyAsync(d_ids, ids, n * sizeof(uint32_t), cudaMemcpyHostToDevice, e.stream));
+      SAM_XG(xg_extract_miss_data(d_rows, h_feat, d_ids, nullptr, n, row_bytes, e.stream));
+      SAM_CUDA(cudaStreamSynchronize(e.stream));
+      cudaFree(d_ids);
+    }
+    return d_rows;
+  };
+  if (n_rep) {
+    e.store.replica = gather_rows_to_device(ranks.data(), n_rep);
+    e.store.num_replicated = (uint32_t)n_rep;
+  }
   const int w = e.worker_id;
   std::vector<void *> mine(P, nullptr);
   const int my_parts = parted ? e.shared->num_parts[w] : 1;
   for (int k = 0; k < my_parts; ++k) {
     const uint32_t p = parted ? (uint32_t)e.shared->part_ids[w][k] : 0u;
     std::vector<uint32_t> ids;
-    for (size_t r = p; r < n_cached; r += P) ids.push_back(ranks[r]);  // rank r -> part r % P, row r / P
-    void *d_part = dev_alloc(e, std::max<size_t>(ids.size() * row_bytes, 16));
-    if (!ids.empty()) {
-      uint32_t *d_ids = nullptr;
-      SAM_CUDA(cudaMalloc(&d_ids, ids.size() * sizeof(uint32_t)));
-      SAM_CUDA(cudaMemcpyAsync(d_ids, ids.data(), ids.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, e.stream));
-      // CPUExtract + H2D in the reference; here the GPU gathers the rows straight out of the host mapping
-      SAM_XG(xg_extract_miss_data(d_part, h_feat, d_ids, nullptr, ids.size(), row_bytes, e.stream));
-      SAM_CUDA(cudaStreamSynchronize(e.stream));
-      cudaFree(d_ids);
-    }
+    for (size_t r = n_rep + p; r < n_cached; r += P) ids.push_back(ranks[r]);  // rank r' = r - n_rep -> part r' % P, row r' / P
+    void *d_part = gather_rows_to_device(ids.data(), ids.size());
     mine[p] = d_part;
     e.store.local_part_mask |= 1u << p;
     if (parted) SAM_XG(xg_ipc_export(d_part, e.shared->feat[w][p]));
@@ -745,6 +759,9 @@ void samgraph_config(const char **keys, const char **vals, const size_t n) {
   c.num_epoch = std::stoull(m["num_epoch"]);
   c.cache_policy = std::stoi(m["_cache_policy"]);
   c.cache_percentage = std::stod(m["cache_percentage"]);
+  if (m.count("ggms_replicate_percentage")) c.replicate_percentage = std::stod(m["ggms_replicate_percentage"]);
+  else if (const char *rp = std::getenv("SAMGRAPH_GGMS_REPLICATE")) c.replicate_percentage = std::atof(rp);
+  SAM_CHECK(c.replicate_percentage >= 0.0 && c.replicate_percentage <= 1.0);
   c.omp_thread_num = std::stoi(m["omp_thread_num"]);
   c.num_layer = std::stoull(m["num_layer"]);
   switch (c.run_arch) {
