@@ -84,7 +84,9 @@ enum {
   SAMGRAPH_TENSOR_INPUT_NODES = 5,  /* [num_input] i32, sampler device                        (adapter.cc:165-178)*/
   SAMGRAPH_TENSOR_OUTPUT_NODES = 6, /* [num_output] i32, sampler device                       (adapter.cc:180-193)*/
   SAMGRAPH_TENSOR_DATASET_FEAT = 7, /* [num_node, feat_dim], host                             (adapter.cc:137-150)*/
-  SAMGRAPH_TENSOR_DATASET_LABEL = 8 /* [num_node] i64, host                                   (adapter.cc:152-163)*/
+  SAMGRAPH_TENSOR_DATASET_LABEL = 8,/* [num_node] i64, host                                   (adapter.cc:152-163)*/
+  SAMGRAPH_TENSOR_CSC_INDPTR = 9    /* [num_dst + 1] i32, layer; KHop0/2/3 only.  (indptr, ROW) is the block in CSC
+                                       form: replaces DGL's COO -> CSC conversion behind adapter.py:98-124        */
 };
 typedef struct samgraph_tensor_view {
   void *data;

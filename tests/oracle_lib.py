@@ -206,6 +206,18 @@ def extract_ggms(feat, nodes, table, parts):
     return out
 
 
+def coo_to_csc_indptr(col, num_dst):
+    """What the caller-side conversion computes from the COO the reference hands over (torch/adapter.py:98-103,
+    create_unitgraph_from_coo(..., ['coo','csr','csc']) -> DGL's COOToCSR on the destination axis): a counting
+    sort's offsets.  For node-major edges the sort is the identity, so (indptr, row) IS the CSC form."""
+    col = u32(col)
+    counts = np.bincount(col, minlength=num_dst).astype(np.uint32)
+    indptr = np.zeros(num_dst + 1, np.uint32)
+    np.cumsum(counts, out=indptr[1:])
+    assert len(col) == 0 or np.all(col[1:] >= col[:-1]), "edges are not destination-major"
+    return indptr
+
+
 def hybrid_placement(feat, rank_nodes, num_cached, num_replicated, num_part):
     """Two-tier GGMS placement (B200 extension, include/xgnn_b200.h xg_feature_store): cache ranks
     [0, num_replicated) form the replica every GPU holds; rank r >= num_replicated goes to part

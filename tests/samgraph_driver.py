@@ -86,6 +86,12 @@ def check_batch(sam, g, key, seeds, fan, sample_type):
         assert sam.get_graph_num_edge(key, l) == len(ref["row"][l])
         if weighted:
             assert np.array_equal(u32(blk[4]), ref["data"][l]), f"layer {l} data"
+        if sample_type in (sam.kKHop0, sam.kKHop2, sam.kKHop3):
+            ip = sam.get_graph_csc_indptr(key, l)
+            assert np.array_equal(u32(ip), O.coo_to_csc_indptr(ref["col"][l], ref["num_dst"][l])), f"layer {l} csc"
+    if sample_type in (sam.kKHop0, sam.kKHop2, sam.kKHop3):
+        cblocks, _, _ = sam.get_dgl_blocks_csc(key, len(fan), with_feat=False)
+        assert len(cblocks) == len(fan)
     assert feat.dtype == torch.float32 and feat.cpu().numpy().tobytes() == g["feat"][ref["input_nodes"]].tobytes(), "feat"
     assert np.array_equal(label.cpu().numpy(), g["label"][seeds]), "label"
     return feat  # the caller may hold it across batches (ownership test)

@@ -61,6 +61,8 @@ def check_minibatch_properties(mb, st, D, seeds_np, fanout, uniform=True):
             want = torch.clamp(deg, max=fanout[l])
             got = torch.bincount(col, minlength=mb.num_dst[l])
             assert torch.equal(got, want)
+            ip = _u32(mb.csc_indptr(l))  # CSC offsets == exclusive scan of the per-node counts
+            assert int(ip[0]) == 0 and torch.equal(ip[1:] - ip[:-1], want)
         # membership of a sample of edges in the CSR list of their source node
         g = torch.Generator(device="cpu").manual_seed(l)
         pick = torch.randint(0, row.numel(), (400,), generator=g).to(dev)

@@ -185,3 +185,18 @@ def test_two_tier_placement_oracle_reads_the_same_rows():
         if nrep == 0 and ncached:  # degenerates to the reference's single-tier routing
             ref_parts = [O.partition_features(feat, rank, ncached, p, P) for p in range(P)]
             assert all(np.array_equal(a, b) for a, b in zip(parts, ref_parts))
+
+
+def test_csc_indptr_oracle_matches_scipy_conversion():
+    """coo_to_csc_indptr restates the caller-side COO -> CSC conversion: check it against scipy's."""
+    import scipy.sparse as sp
+    rng = np.random.default_rng(2)
+    num_dst, num_src = 50, 400
+    counts = rng.integers(0, 7, num_dst)
+    col = np.repeat(np.arange(num_dst), counts).astype(np.uint32)  # node-major
+    row = rng.integers(0, num_src, len(col)).astype(np.uint32)
+    indptr = O.coo_to_csc_indptr(col, num_dst)
+    m = sp.coo_matrix((np.ones(len(col)), (row, col)), shape=(num_src, num_dst)).tocsc()
+    assert np.array_equal(indptr, m.indptr.astype(np.uint32))
+    for d in range(num_dst):  # same neighbour multiset per destination
+        assert sorted(row[indptr[d]:indptr[d + 1]].tolist()) == sorted(row[col == d].tolist())

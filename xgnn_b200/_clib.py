@@ -84,6 +84,7 @@ class XgBatchView(Structure):
         ("output_nodes", c_void_p),
         ("input_feat", c_void_p),
         ("output_label", c_void_p),
+        ("csc_indptr", c_void_p * XG_MAX_LAYERS),
     ]
 
 

@@ -1120,6 +1120,12 @@ void samgraph_get_graph_tensor(uint64_t key, int which, int layer, samgraph_tens
       out->shape[0] = (int64_t)v.num_edge[layer];
       break;
     }
+    case SAMGRAPH_TENSOR_CSC_INDPTR:
+      SAM_CHECK(layer >= 0 && (uint32_t)layer < v.num_layer);
+      SAM_CHECK_MSG(v.csc_indptr[layer] != nullptr, "CSC offsets exist for KHop0/KHop2/KHop3 only (node-major edges)");
+      out->data = const_cast<uint32_t *>(v.csc_indptr[layer]);
+      out->shape[0] = (int64_t)v.num_dst[layer] + 1;
+      break;
     case SAMGRAPH_TENSOR_INPUT_NODES:
       out->data = const_cast<uint32_t *>(v.input_nodes);
       out->shape[0] = v.num_input;

@@ -49,14 +49,6 @@ __global__ void collect_counts_kernel(TableView t, int num_fill, BatchCounts *ou
   if (i == 0) out->overflow = *t.overflow;
 }
 
-__global__ void __launch_bounds__(256)
-copy_ids_kernel(uint32_t *__restrict__ dst, const uint32_t *__restrict__ src, size_t n_max,
-                const uint32_t *__restrict__ d_n) {
-  size_t n = *d_n < n_max ? *d_n : n_max;
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    dst[i] = src[i];
-}
-
 size_t elem_bytes(int dtype) {
   switch (dtype) {
     case XG_F32: case XG_I32: return 4;
@@ -76,6 +68,7 @@ struct xg_batch {
   // device
   uint32_t *seeds = nullptr, *seed_local = nullptr, *input_nodes = nullptr;
   uint32_t *row[XG_MAX_LAYERS] = {}, *col[XG_MAX_LAYERS] = {}, *data[XG_MAX_LAYERS] = {};
+  uint32_t *csc_indptr[XG_MAX_LAYERS] = {};  // uniform samplers only: [cap_in[l] + 1]
   void *feat = nullptr;
   int64_t *label = nullptr;
   BatchParams *d_params = nullptr;
@@ -153,6 +146,10 @@ int alloc_slot(xg_sampler *s, xg_batch **out) {
     XG_CUDA(cudaMalloc(&b->row[l], s->cap_edge[l] * sizeof(uint32_t)));
     XG_CUDA(cudaMalloc(&b->col[l], s->cap_edge[l] * sizeof(uint32_t)));
     if (s->cfg.sample_type == XG_RANDOM_WALK) XG_CUDA(cudaMalloc(&b->data[l], s->cap_edge[l] * sizeof(uint32_t)));
+    if (s->uniform) {
+      XG_CUDA(cudaMalloc(&b->csc_indptr[l], (s->cap_in[l] + 1) * sizeof(uint32_t)));
+      XG_CUDA(cudaMemset(b->csc_indptr[l], 0, sizeof(uint32_t)));  // an empty layer still has indptr[0] = 0
+    }
   }
   if (s->has_store) XG_CUDA(cudaMalloc(&b->feat, s->cap_input * s->row_bytes));
   if (s->label) XG_CUDA(cudaMalloc(&b->label, B * sizeof(int64_t)));
@@ -190,6 +187,7 @@ void free_slot(xg_batch *b) {
     cudaFree(b->row[l]);
     cudaFree(b->col[l]);
     cudaFree(b->data[l]);
+    cudaFree(b->csc_indptr[l]);
   }
   cudaFree(b->feat);
   cudaFree(b->label);
@@ -210,7 +208,12 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
   cudaStream_t st = s->stream;
   const int L = (int)s->cfg.num_layer;
   const size_t B = s->cfg.batch_size;
-  const TableView &t = s->view;
+  // the table's unique list (n2o) IS this slot's input_nodes buffer: the numbering kernels append straight into
+  // it, so task->input_nodes needs no copy and the next batch (another slot) cannot overwrite it while the
+  // extract phase of this one is still reading
+  TableView t = s->view;
+  t.n2o = b->input_nodes;
+  t.n2o_cap = (uint32_t)s->cap_input;
   const uint64_t *d_nseed64 = &b->d_params->num_seeds;
   const uint32_t *d_nseed32 = &b->d_params->num_seeds32;
 
@@ -244,6 +247,7 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
       fusion.table = t;
       fusion.pos_out = s->pos;
       fusion.src_local = src_local;
+      fusion.csc_indptr = b->csc_indptr[l];
       fusion.enabled = true;
       rc = launch_sample_uniform(s->graph, in_nodes, s->cap_in[l], d_num_in, s->cfg.fanout[l], b->col[l], s->dst_global,
                                  d_num_edge, 0, 0, &b->d_params->rng_key, salt, fusion, scan_a(s), st);
@@ -272,10 +276,7 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
     mark();
   }
 
-  // task->input_nodes = the unique list (dist_loops.cc:357); counts leave the table before the next Reset
-  copy_ids_kernel<<<grid_for((s->cap_input + 255) / 256, 4), 256, 0, st>>>(b->input_nodes, t.n2o, s->cap_input,
-                                                                         &t.items[L + 1]);
-  XG_LAUNCHED();
+  // task->input_nodes = the unique list (dist_loops.cc:357), already in place; counts leave the table before the next Reset
   collect_counts_kernel<<<1, 32, 0, st>>>(t, L + 1, b->d_counts);
   XG_LAUNCHED();
   mark();
@@ -626,6 +627,7 @@ int xg_batch_wait(xg_batch *b, xg_batch_view *view) {
     view->row[l] = b->row[l];
     view->col[l] = b->col[l];
     view->data[l] = b->data[l];
+    view->csc_indptr[l] = b->csc_indptr[l];
     view->num_dst[l] = (l == L - 1) ? b->num_seeds : c.items[fill - 1];  // num_dst = num_input (dist_loops.cc:304-306)
     view->num_src[l] = c.items[fill];
     view->num_edge[l] = c.num_edge[l];

@@ -91,6 +91,12 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
     }
     __syncthreads();
     const uint64_t tile_base = s_tile_base;
+    if (FUSED && fusion.csc_indptr != nullptr) {
+      // edges are node-major in input order, so the compacted offset of node i is indptr[i] of the layer's CSC
+      // (destination-major) form: the caller can build the DGL block without a COO -> CSC conversion
+      if (i < n) fusion.csc_indptr[i] = (uint32_t)(tile_base + excl);
+      if (i == n - 1) fusion.csc_indptr[n] = (uint32_t)(tile_base + excl + cnt);
+    }
 
     // ---------------- phase B: G lanes per node ---------------------------------------------
     if constexpr (VPL == 1 && PIPE) {

@@ -17,6 +17,7 @@ struct SampleFusion {
   TableView table;
   uint32_t *pos_out;          // [num_input * fanout]
   const uint32_t *src_local;  // local id of input[i], or NULL for identity
+  uint32_t *csc_indptr;       // [num_input + 1] or NULL: edge offset of every input node = the block's CSC indptr
   bool enabled;
 };
 

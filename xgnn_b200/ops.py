@@ -318,6 +318,12 @@ class Minibatch:
         """per-edge payload (random-walk visit counts), samgraph_torch_get_graph_data"""
         return self._t(self.view.data[l], (self.num_edge[l],), torch.int32) if self.view.data[l] else None
 
+    def csc_indptr(self, l):
+        """[num_dst + 1] edge offsets of the layer's destination nodes (KHop0/2/3), else None: with row(l) as the
+        indices array this is the block in CSC form (no COO -> CSC conversion on the caller side)."""
+        p = self.view.csc_indptr[l]
+        return self._t(p, (self.num_dst[l] + 1,), torch.int32) if p else None
+
     def timeline(self):
         """XG_TIMELINE=1: ms since sampler creation of (sample begin, sample end, extract begin, extract end)."""
         ms = (ctypes.c_float * 4)()

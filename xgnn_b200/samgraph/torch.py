@@ -17,7 +17,7 @@ from .common import *  # noqa: F401,F403
 from .common import _basics
 
 (TENSOR_FEAT, TENSOR_LABEL, TENSOR_ROW, TENSOR_COL, TENSOR_DATA, TENSOR_INPUT_NODES, TENSOR_OUTPUT_NODES,
- TENSOR_DATASET_FEAT, TENSOR_DATASET_LABEL) = range(9)
+ TENSOR_DATASET_FEAT, TENSOR_DATASET_LABEL, TENSOR_CSC_INDPTR) = range(10)
 
 
 class _TensorView(ctypes.Structure):  # samgraph_tensor_view, include/samgraph_abi.h
@@ -160,6 +160,35 @@ def get_dgl_blocks(batch_key, num_layers, with_feat=True):
     for i in range(num_layers):
         row, col = get_graph_row(batch_key, i), get_graph_col(batch_key, i)
         blocks.append(_create_dgl_block((row, col), get_graph_num_src(batch_key, i), get_graph_num_dst(batch_key, i)))
+    return blocks, feat, label
+
+
+def get_graph_csc_indptr(batch_key, layer_idx):
+    """[num_dst + 1] int32 edge offsets of the layer's destination nodes (KHop0/KHop2/KHop3): with
+    get_graph_row() as the indices array the block is already in CSC form."""
+    return _tensor(batch_key, TENSOR_CSC_INDPTR, layer_idx)
+
+
+def _create_dgl_block_csc(indptr, indices, num_src_nodes, num_dst_nodes):
+    """hand DGL the destination-major form directly (dgl.create_block with a 'csc' tuple) so
+    that message passing needs no COO -> CSC conversion (kLogL1ConvertTime of the reference's loops).
+    Without DGL the CSC triple is returned."""
+    try:
+        import dgl
+    except ImportError:
+        return (indptr, indices, num_src_nodes, num_dst_nodes)
+    return dgl.create_block(('csc', (indptr, indices, torch.empty(0, dtype=indices.dtype, device=indices.device))),
+                            num_src_nodes=num_src_nodes, num_dst_nodes=num_dst_nodes)
+
+
+def get_dgl_blocks_csc(batch_key, num_layers, with_feat=True):
+    """get_dgl_blocks (adapter.py:105-124) with every block built from the sampler's own CSC offsets."""
+    feat = get_graph_feat(batch_key) if with_feat else None
+    label = get_graph_label(batch_key) if with_feat else None
+    blocks = []
+    for i in range(num_layers):
+        blocks.append(_create_dgl_block_csc(get_graph_csc_indptr(batch_key, i), get_graph_row(batch_key, i),
+                                            get_graph_num_src(batch_key, i), get_graph_num_dst(batch_key, i)))
     return blocks, feat, label
 
 
