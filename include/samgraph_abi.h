@@ -86,7 +86,8 @@ enum {
   SAMGRAPH_TENSOR_DATASET_FEAT = 7, /* [num_node, feat_dim], host                             (adapter.cc:137-150)*/
   SAMGRAPH_TENSOR_DATASET_LABEL = 8,/* [num_node] i64, host                                   (adapter.cc:152-163)*/
   SAMGRAPH_TENSOR_CSC_INDPTR = 9    /* [num_dst + 1] i32, layer; KHop0/2/3 only.  (indptr, ROW) is the block in CSC
-                                       form: replaces DGL's COO -> CSC conversion behind adapter.py:98-124        */
+                                       form: replaces DGL's COO -> CSC conversion behind adapter.py:98-124;
+                                       data == NULL when the layer has none (other samplers, duplicate seeds)     */
 };
 typedef struct samgraph_tensor_view {
   void *data;

@@ -274,7 +274,8 @@ typedef struct xg_batch_view {
   const uint32_t *output_nodes;
   const void *input_feat;      /* [num_input, feat_dim] or NULL when no feature store was given */
   const int64_t *output_label; /* [num_output] or NULL */
-  /* KHop0/2/3 only (edges node-major in input order), else NULL: csc_indptr[l][0..num_dst[l]] are the edge offsets
+  /* KHop0/2/3 only (edges node-major in input order), else NULL (also NULL for the seed layer of a batch whose
+     seeds contain duplicates: they share a local id, so that layer is not destination-major): csc_indptr[l][0..num_dst[l]] are the edge offsets
      of the layer's destination nodes, i.e. (csc_indptr, row) is the block in CSC form - what DGL's
      create_unitgraph_from_coo + format conversion computes on the caller side (torch/adapter.py:98-124). */
   const uint32_t *csc_indptr[XG_MAX_LAYERS];

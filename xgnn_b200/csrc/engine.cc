@@ -1122,9 +1122,9 @@ void samgraph_get_graph_tensor(uint64_t key, int which, int layer, samgraph_tens
     }
     case SAMGRAPH_TENSOR_CSC_INDPTR:
       SAM_CHECK(layer >= 0 && (uint32_t)layer < v.num_layer);
-      SAM_CHECK_MSG(v.csc_indptr[layer] != nullptr, "CSC offsets exist for KHop0/KHop2/KHop3 only (node-major edges)");
+      // NULL data = no CSC form (weighted / KHop1 samplers, or a seed layer with duplicate seeds): use ROW/COL
       out->data = const_cast<uint32_t *>(v.csc_indptr[layer]);
-      out->shape[0] = (int64_t)v.num_dst[layer] + 1;
+      out->shape[0] = v.csc_indptr[layer] ? (int64_t)v.num_dst[layer] + 1 : 0;
       break;
     case SAMGRAPH_TENSOR_INPUT_NODES:
       out->data = const_cast<uint32_t *>(v.input_nodes);

@@ -627,7 +627,10 @@ int xg_batch_wait(xg_batch *b, xg_batch_view *view) {
     view->row[l] = b->row[l];
     view->col[l] = b->col[l];
     view->data[l] = b->data[l];
-    view->csc_indptr[l] = b->csc_indptr[l];
+    // duplicate seeds (the aligned shuffler's padding, dist_shuffler_aligned.cc:53-55) share one local id, so the
+    // seed layer's edges are then not destination-major: no CSC form for that layer of that batch
+    const bool dup_seeds = (l == L - 1) && c.items[1] != b->num_seeds;
+    view->csc_indptr[l] = dup_seeds ? nullptr : b->csc_indptr[l];
     view->num_dst[l] = (l == L - 1) ? b->num_seeds : c.items[fill - 1];  // num_dst = num_input (dist_loops.cc:304-306)
     view->num_src[l] = c.items[fill];
     view->num_edge[l] = c.num_edge[l];

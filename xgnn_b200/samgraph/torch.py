@@ -166,7 +166,8 @@ def get_dgl_blocks(batch_key, num_layers, with_feat=True):
 def get_graph_csc_indptr(batch_key, layer_idx):
     """[num_dst + 1] int32 edge offsets of the layer's destination nodes (KHop0/KHop2/KHop3): with
     get_graph_row() as the indices array the block is already in CSC form."""
-    return _tensor(batch_key, TENSOR_CSC_INDPTR, layer_idx)
+    t = _tensor(batch_key, TENSOR_CSC_INDPTR, layer_idx)
+    return t if t is not None and t.numel() > 0 else None
 
 
 def _create_dgl_block_csc(indptr, indices, num_src_nodes, num_dst_nodes):
@@ -187,8 +188,12 @@ def get_dgl_blocks_csc(batch_key, num_layers, with_feat=True):
     label = get_graph_label(batch_key) if with_feat else None
     blocks = []
     for i in range(num_layers):
-        blocks.append(_create_dgl_block_csc(get_graph_csc_indptr(batch_key, i), get_graph_row(batch_key, i),
-                                            get_graph_num_src(batch_key, i), get_graph_num_dst(batch_key, i)))
+        indptr = get_graph_csc_indptr(batch_key, i)
+        nsrc, ndst = get_graph_num_src(batch_key, i), get_graph_num_dst(batch_key, i)
+        if indptr is None:  # no CSC form for this layer (see include/samgraph_abi.h): the reference's COO block
+            blocks.append(_create_dgl_block((get_graph_row(batch_key, i), get_graph_col(batch_key, i)), nsrc, ndst))
+        else:
+            blocks.append(_create_dgl_block_csc(indptr, get_graph_row(batch_key, i), nsrc, ndst))
     return blocks, feat, label
 
 
