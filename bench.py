@@ -273,7 +273,8 @@ def run_reference(args):
 
 def placement_note(args, world, V, row_bytes):
     if world == 1:
-        return "GGMS: topology + features in 1 GPU's HBM, cache 100%"
+        return ("GGMS: topology + features in 1 GPU's HBM, cache 100% (one part, laid out by node id: no cache-table "
+                "lookup; partial caches and N > 1 go through the direct-address table)")
     rep = args.replicate
     gb = V * row_bytes / 1e9
     if rep <= 0:

@@ -80,11 +80,11 @@ def check_minibatch_properties(mb, st, D, seeds_np, fanout, uniform=True):
     assert torch.equal(mb.label, seeds % st.num_class)
 
 
-def _run(shape, scale, batches=3, cache_pct=1.0, host_rows=False, need_gb=0.0, **sampler_kw):
+def _run(shape, scale, batches=3, cache_pct=1.0, host_rows=False, need_gb=0.0, flat=True, **sampler_kw):
     D, ops = _lazy()
     if _free_gb() < need_gb:
         pytest.skip(f"needs {need_gb:.0f} GB of free HBM")
-    st = D.build_store(shape, 0, 0, 1, scale=scale, cache_pct=cache_pct)
+    st = D.build_store(shape, 0, 0, 1, scale=scale, cache_pct=cache_pct, flat_when_full=flat)
     host = None
     if host_rows:  # cold rows served from pinned host memory over UVA (GPUExtractMissData path)
         host = torch.empty((st.num_node, st.dim), dtype=st.dtype).pin_memory()
@@ -113,7 +113,7 @@ def test_cfg2_papers100M_full_size():
 
 def test_cfg3_twitter_full_size():
     """configs[2]: 41.7 M nodes, 1.5 B edges, 256 x fp32 (42.6 GB of rows)."""
-    _run("twitter", 1, need_gb=80)
+    _run("twitter", 1, need_gb=80, flat=False)  # through the direct-address cache table (rank-ordered part)
 
 
 def test_cfg1_products_full_size_khop3():

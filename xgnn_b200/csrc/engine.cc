@@ -551,6 +551,16 @@ void build_feature_store(Engine &e) {
   if (n_cached == 0) return;                                          // cache_table == NULL: every row from `host`
   const bool parted = cfg.run_arch == kArch6 && cfg.part_cache && e.shared != nullptr;
   const uint32_t P = parted ? (uint32_t)e.shared->num_worker : 1u;
+  if (!parted && n_cached == V) {
+    // every row cached in one part: lay the part out by node id (where a cached row sits is ours to choose) and
+    // skip the direct-address table - no 4-byte random lookup (a 128-byte DRAM line each) in front of every row
+    const void *h = pin_host(ds.feat, V * row_bytes);
+    void *d_all = dev_alloc(e, V * row_bytes);
+    SAM_CUDA(cudaMemcpyAsync(d_all, h, V * row_bytes, cudaMemcpyHostToDevice, e.stream));
+    SAM_CUDA(cudaStreamSynchronize(e.stream));
+    e.store.host = d_all;  // "host" slot of the handle = the flat table, wherever it lives
+    return;
+  }
   std::vector<uint32_t> ranks(ds.ranking, ds.ranking + n_cached);
   // two-tier store (B200 extension, config key `ggms_replicate_percentage`, default 0 = the reference layout): the
   // hottest ranks keep the policy order and are replicated per GPU; only the sharded remainder is shuffled

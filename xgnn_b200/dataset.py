@@ -108,7 +108,8 @@ def cache_rank_nodes(num_node: int, num_cached: int, num_replicated: int = 0) ->
 
 
 def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale: int = 1, cache_pct: float = 1.0,
-                replicate_pct: float = 0.0, with_features: bool = True, seed: int = SYNTH_SEED) -> GGMSStore:
+                replicate_pct: float = 0.0, with_features: bool = True, seed: int = SYNTH_SEED,
+                flat_when_full: bool = True) -> GGMSStore:
     """Generate THIS rank's shards (topology part `rank`, feature part `rank`) of the named shape,
     scaled down by `scale`. Peer parts are attached afterwards (attach_peers) from IPC handles."""
     V, E, dim, dtype, num_class, train_frac = SHAPES[shape]
@@ -123,7 +124,14 @@ def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale
         indptr, indices, ne = gen_csr(rank, P, n_part, V, c, seed, dev)
         st.local.update(indptr=indptr, indices=indices, num_local_edge=ne)
         st.label = (torch.arange(V, dtype=torch.int64, device=dev) % num_class)
-        if with_features:
+        if with_features and P == 1 and cache_pct >= 1.0 and flat_when_full:
+            # one part holding every row: WHERE a cached row is stored is ours to choose ("GGMS routing must
+            # match in which row is read, not in where it is stored"), so the single part is laid out by node id and
+            # the direct-address table (4 B x V, one 128-byte DRAM line per random lookup) is not needed at all
+            st.local["feat_part"] = gen_features(V, dim, dtype, dev, begin=0)
+            st.local["num_cached"] = V
+            st.local["flat"] = True
+        elif with_features:
             n_cached = int(V * cache_pct)
             n_rep = min(n_cached, int(V * replicate_pct)) if P > 1 else 0
             ranks = cache_rank_nodes(V, n_cached, n_rep)
@@ -154,7 +162,9 @@ def attach(st: GGMSStore, part_indptr=None, part_indices=None, feat_parts=None, 
         feat_parts = [st.local.get("feat_part")]
     st.graph = ops.make_graph(part_indptr=part_indptr, part_indices=part_indices, num_cache_node=st.num_node,
                               num_node=st.num_node, host_indptr=None, host_indices=None)
-    if st.local.get("cache_table") is not None:
+    if st.local.get("flat"):
+        st.store = ops.make_feature_store(st.row_bytes, st.local["feat_part"], None)
+    elif st.local.get("cache_table") is not None:
         st.store = ops.make_feature_store(st.row_bytes, host_feat, st.local["cache_table"], parts=feat_parts,
                                           local_parts=(st.rank,), replica=st.local.get("replica"),
                                           num_replicated=st.local.get("num_replicated", 0))
