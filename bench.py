@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-steps", type=int, default=20, help="steps of the per-stage CUDA-event pass")
-    ap.add_argument("--replicate", type=float, default=float(os.environ.get("XG_BENCH_REPLICATE", "0.5")),
+    ap.add_argument("--replicate", type=float, default=float(os.environ.get("XG_BENCH_REPLICATE", "0.6")),
                     help="N > 1 only: fraction of the nodes (hottest first, by degree rank) whose feature rows every GPU "
                          "keeps in its own HBM; the rest is sharded rank %% P (0 = the reference's pure sharding)")
     return ap.parse_args()
