@@ -334,6 +334,16 @@ int xg_ipc_import(const unsigned char handle[64], void **out);
 int xg_ipc_close(void *p);
 int xg_enable_peer_access(int device, int peer);
 
+/* Presampling cache-rank policy (kCacheByPreSample): dist::PreSampler, dist/pre_sampler.cc:40-165.
+ * accumulate: freq[v] += 1 for every v of one batch's input_nodes (count from *d_num_nodes when given, else
+ * num_nodes_max).  rank: nodes ordered by frequency descending, ties by node id descending - the order of
+ * __gnu_parallel::sort(std::greater<>) over {low: id, high: freq} words (pre_sampler.cc:113-119); d_rank_freq may be
+ * NULL (GetFreq, :131-139).  rank synchronises the stream. */
+int xg_presample_accumulate(uint32_t *d_freq, uint32_t num_node, const uint32_t *d_nodes, size_t num_nodes_max,
+                            const uint32_t *d_num_nodes, void *stream);
+int xg_presample_rank(const uint32_t *d_freq, uint32_t num_node, uint32_t *d_rank_nodes, uint32_t *d_rank_freq,
+                      void *stream);
+
 /* DistAlignedShuffler::ReShuffle, dist/dist_shuffler_aligned.cc:75-121: one epoch's Fisher-Yates pass with
  * std::default_random_engine(seed = epoch), in place over the padded train set (host memory).  The engine
  * applies it epoch after epoch to the same array, as the reference does. */

@@ -206,6 +206,17 @@ def extract_ggms(feat, nodes, table, parts):
     return out
 
 
+def presample_rank(num_node, input_node_lists):
+    """dist::PreSampler (dist/pre_sampler.cc:76-152): freq[v] = number of batches whose input_nodes contain v;
+    ranking = sort of the 64-bit words {low: id, high: freq} with std::greater (freq desc, then id desc)."""
+    freq = np.zeros(num_node, np.uint64)
+    for nodes in input_node_lists:
+        freq[u32(nodes)] += 1
+    words = (freq << np.uint64(32)) | np.arange(num_node, dtype=np.uint64)
+    words = np.sort(words)[::-1]
+    return (words & np.uint64(0xFFFFFFFF)).astype(np.uint32), (words >> np.uint64(32)).astype(np.uint32)
+
+
 def coo_to_csc_indptr(col, num_dst):
     """What the caller-side conversion computes from the COO the reference hands over (torch/adapter.py:98-103,
     create_unitgraph_from_coo(..., ['coo','csr','csc']) -> DGL's COOToCSR on the destination axis): a counting

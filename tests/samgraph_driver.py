@@ -50,6 +50,8 @@ def run_config(sam, d, sample_type, g, arch, extra):
         fan = [maxdeg, maxdeg] if sample_type in (sam.kKHop0, sam.kKHop3, sam.kKHop2) else [4, 6]
         cfg.update(fanout=fan, num_fanout=2)
     cfg.update(extra)
+    if os.environ.get("XG_TEST_PRESAMPLE"):  # cache ranking from presampling instead of cache_by_degree.bin
+        cfg.update(_cache_policy=sam.kCacheByPreSample, presample_epoch=int(os.environ["XG_TEST_PRESAMPLE"]))
     sam.config(cfg)
     return fan
 

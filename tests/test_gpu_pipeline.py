@@ -198,3 +198,20 @@ def test_minibatch_other_samplers_bit_exact_vs_oracle_replay(ops, wgraph, sample
         assert mb.feat.cpu().numpy().tobytes() == wgraph["feat"][ref["input_nodes"]].tobytes()
         assert np.array_equal(mb.label.cpu().numpy(), wgraph["label"][seeds])
         mb.release()
+
+
+def test_presample_rank_bit_exact_vs_oracle(ops, small):
+    """kCacheByPreSample ranking (dist/pre_sampler.cc): with fanout >= degree the batches are deterministic, so the
+    frequency table and the (freq desc, id desc) order must equal the oracle's bit for bit."""
+    g = ops.make_graph(dev(small["indptr"]), dev(small["indices"]))
+    fan = [small["maxdeg"], small["maxdeg"]]
+    B = 200
+    sm = ops.MinibatchSampler(g, fan, B, seed=5, max_input_nodes=small["V"] + B)
+    train = synth.train_set(small["V"], 0.1)
+    batches = [train[o:o + B] for o in range(0, len(train), B)]
+    rank_nodes, rank_freq = ops.presample_rank(sm, small["V"], batches)
+    lists = [O.minibatch(small["indptr"], small["indices"], b, fan, seed=1)["input_nodes"] for b in batches]
+    want_nodes, want_freq = O.presample_rank(small["V"], lists)
+    assert np.array_equal(u32(rank_freq), want_freq)
+    assert np.array_equal(u32(rank_nodes), want_nodes)
+    assert want_freq[0] >= want_freq[-1] and sorted(want_nodes.tolist()) == list(range(small["V"]))

@@ -200,3 +200,9 @@ def test_csc_indptr_oracle_matches_scipy_conversion():
     assert np.array_equal(indptr, m.indptr.astype(np.uint32))
     for d in range(num_dst):  # same neighbour multiset per destination
         assert sorted(row[indptr[d]:indptr[d + 1]].tolist()) == sorted(row[col == d].tolist())
+
+
+def test_presample_rank_oracle_order():
+    """freq descending, ties by node id descending (std::greater on {low: id, high: freq}, pre_sampler.cc:113-119)"""
+    nodes, freq = O.presample_rank(6, [np.array([1, 3], np.uint32), np.array([3, 4], np.uint32), np.array([3, 1], np.uint32)])
+    assert nodes.tolist() == [3, 1, 4, 5, 2, 0] and freq.tolist() == [3, 2, 1, 0, 0, 0]

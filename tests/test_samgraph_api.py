@@ -117,3 +117,12 @@ def test_arch6_two_tier_feature_store(dataset, sample_type, workers, rep):
     import torch
     _drive("arch6", dataset, sample_type, workers,
            env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "SAMGRAPH_GGMS_REPLICATE": str(rep)})
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,args", [("single", (0,)), ("arch6", (7, 2))])
+def test_presample_cache_policy_flows(dataset, mode, args):
+    """kCacheByPreSample: worker 0 ranks the nodes by presampled access frequency at sample_init (on the GPU), every
+    trainer builds its cache from that ranking; batches must still carry CPUExtract's rows bit for bit."""
+    import torch
+    _drive(mode, dataset, *args, env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "XG_TEST_PRESAMPLE": "1"})

@@ -110,6 +110,7 @@ struct RunConfig {
   int run_arch = 0, sample_type = 0, cache_policy = 0;
   size_t batch_size = 0, num_epoch = 0, num_layer = 0;
   double cache_percentage = 0.0;
+  int presample_epoch = 0;            // operation.cc:184-189
   double replicate_percentage = 0.0;  // `ggms_replicate_percentage`: hot tier replicated per GPU (0 = reference layout)
   std::vector<size_t> fanout;
   size_t random_walk_length = 0, num_random_walk = 0, num_neighbor = 0;
@@ -143,6 +144,7 @@ struct Dataset {
   const int64_t *label = nullptr;
   const float *prob = nullptr, *prefix = nullptr;
   std::vector<uint32_t> ranking_owned;
+  uint32_t *ranking_rw = nullptr;  // kCacheByPreSample: shared, written by worker 0 at sample_init
   std::vector<Mapping> maps;
   size_t feat_row_bytes() const { return feat_dim * (feat_dtype == XG_F16 ? 2 : feat_dtype == XG_F64 ? 8 : feat_dtype == XG_U8 ? 1 : 4); }
 };
@@ -226,6 +228,17 @@ void load_dataset(Dataset &ds, const RunConfig &cfg, bool shared) {
   }
   if (cfg.cache_percentage > 0.0) {
     const char *name = nullptr;
+    if (cfg.cache_policy == kCacheByPreSample) {
+      // the ranking is produced at sample_init by worker 0 and read by every trainer (dist_engine.cc:455-466): it
+      // lives in an anonymous shared mapping created before fork, like the reference's ranking_nodes tensor
+      void *mem = ::mmap(nullptr, std::max<size_t>(ds.num_node * 4, 4096), PROT_READ | PROT_WRITE,
+                         MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+      SAM_CHECK(mem != MAP_FAILED);
+      ds.ranking_rw = static_cast<uint32_t *>(mem);
+      std::iota(ds.ranking_rw, ds.ranking_rw + ds.num_node, 0u);
+      ds.ranking = ds.ranking_rw;
+      return;
+    }
     switch (cfg.cache_policy) {
       case kCacheByDegree: name = "cache_by_degree.bin"; break;
       case kCacheByHeuristic: name = "cache_by_heuristic.bin"; break;
@@ -263,7 +276,7 @@ constexpr int kLogL1NumSample = 0, kLogL1NumNode = 1, kLogL1SampleTotalTime = 2,
 constexpr int kLogEpochSampleTime = 0, kLogEpochSampleTotalTime = 3, kLogEpochCopyTime = 8, kLogEpochFeatureBytes = 12,
               kLogEpochNumSample = 15;
 constexpr int kLogInitL1Common = 0, kLogInitL1Sampler = 1, kLogInitL1Trainer = 2, kLogInitL2LoadDataset = 6,
-              kLogInitL2BuildCache = 10;
+              kLogInitL2Presample = 8, kLogInitL2BuildCache = 10;
 
 struct Profiler {
   std::mutex mu;
@@ -705,6 +718,60 @@ void common_device_init(Engine &e, int device) {
   SAM_CUDA(cudaStreamCreateWithFlags(&e.stream, cudaStreamNonBlocking));
 }
 
+// dist::PreSampler::DoPreSample + GetRankNode (dist/pre_sampler.cc:76-152, driven from dist_engine.cc:455-466): worker 0
+// samples `presample_epoch` epochs of the whole train set (no feature extraction), counts on the GPU how many batches
+// need each node, ranks; the other workers wait at the barrier.
+void presample_ranking(Engine &e) {
+  const RunConfig &cfg = g_cfg;
+  Dataset &ds = e.ds;
+  if (cfg.cache_policy != kCacheByPreSample || cfg.cache_percentage <= 0.0 || ds.ranking_rw == nullptr) return;
+  const double t0 = now_s();
+  if (e.worker_id == 0) {
+    xg_sampler_config sc{};
+    sc.num_layer = (uint32_t)cfg.num_layer;
+    for (size_t l = 0; l < cfg.num_layer; ++l) sc.fanout[l] = (uint32_t)cfg.fanout[l];
+    sc.batch_size = (uint32_t)cfg.batch_size;
+    sc.sample_type = cfg.sample_type;
+    sc.num_slots = 2;
+    sc.seed = 0x50524553ull;  // "PRES": its own stream of draws, independent of the training batches
+    sc.stream = e.stream;
+    sc.random_walk_length = (uint32_t)cfg.random_walk_length;
+    sc.num_random_walk = (uint32_t)cfg.num_random_walk;
+    sc.random_walk_restart_prob = cfg.random_walk_restart_prob;
+    sc.prob_table = e.d_prob;
+    sc.alias_table = e.d_alias;
+    sc.prob_prefix_table = e.d_prefix;
+    xg_sampler *ps = nullptr;
+    SAM_XG(xg_sampler_create(&ps, &e.graph, nullptr, nullptr, &sc, e.device));
+    uint32_t *d_freq = nullptr, *d_rank = nullptr;
+    SAM_CUDA(cudaMalloc(&d_freq, ds.num_node * sizeof(uint32_t)));
+    SAM_CUDA(cudaMalloc(&d_rank, ds.num_node * sizeof(uint32_t)));
+    SAM_CUDA(cudaMemsetAsync(d_freq, 0, ds.num_node * sizeof(uint32_t), e.stream));
+    std::vector<uint32_t> order(ds.train_set, ds.train_set + ds.num_train);
+    uint64_t key = 0;
+    for (int ep = 0; ep < cfg.presample_epoch; ++ep) {
+      AlignedShuffler::shuffle_epoch(order, (size_t)ep);
+      for (size_t o = 0; o < order.size(); o += cfg.batch_size) {
+        const size_t n = std::min(cfg.batch_size, order.size() - o);
+        xg_batch *b = nullptr;
+        xg_batch_view v;
+        SAM_XG(xg_sampler_submit(ps, order.data() + o, n, 0, key++, &b));
+        SAM_XG(xg_batch_wait(b, &v));
+        SAM_XG(xg_presample_accumulate(d_freq, (uint32_t)ds.num_node, v.input_nodes, v.num_input, nullptr, e.stream));
+        SAM_CUDA(cudaStreamSynchronize(e.stream));
+        SAM_XG(xg_batch_release(b));
+      }
+    }
+    SAM_XG(xg_presample_rank(d_freq, (uint32_t)ds.num_node, d_rank, nullptr, e.stream));
+    SAM_CUDA(cudaMemcpy(ds.ranking_rw, d_rank, ds.num_node * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    cudaFree(d_freq);
+    cudaFree(d_rank);
+    SAM_XG(xg_sampler_destroy(ps));
+  }
+  barrier(e);
+  g_prof.init[kLogInitL2Presample] = now_s() - t0;
+}
+
 void sampler_side_init(Engine &e) {
   const double t0 = now_s();
   build_topology(e);
@@ -717,6 +784,7 @@ void sampler_side_init(Engine &e) {
   e.shuffler.reset(new AlignedShuffler(e.ds.train_set, e.ds.num_train, g_cfg.num_epoch, g_cfg.batch_size,
                                        (size_t)e.worker_id, g_cfg.num_worker));
   SAM_CHECK(e.shuffler->num_local_step == e.num_local_step);
+  presample_ranking(e);
   e.sampler_ready = true;
   g_prof.init[kLogInitL1Sampler] = now_s() - t0;
 }
@@ -769,6 +837,7 @@ void samgraph_config(const char **keys, const char **vals, const size_t n) {
   c.num_epoch = std::stoull(m["num_epoch"]);
   c.cache_policy = std::stoi(m["_cache_policy"]);
   c.cache_percentage = std::stod(m["cache_percentage"]);
+  if (m.count("presample_epoch")) c.presample_epoch = std::stoi(m["presample_epoch"]);
   if (m.count("ggms_replicate_percentage")) c.replicate_percentage = std::stod(m["ggms_replicate_percentage"]);
   else if (const char *rp = std::getenv("SAMGRAPH_GGMS_REPLICATE")) c.replicate_percentage = std::atof(rp);
   SAM_CHECK(c.replicate_percentage >= 0.0 && c.replicate_percentage <= 1.0);

@@ -434,6 +434,23 @@ class MinibatchSampler:
         return torch.cuda.ExternalStream(int(lib.xg_sampler_extract_stream(self._h) or 0), device=self.device)
 
 
+def presample_rank(sampler: "MinibatchSampler", num_node: int, batches, key0: int = 0):
+    """dist::PreSampler::DoPreSample + GetRankNode/GetFreq (dist/pre_sampler.cc:76-152): run the given seed batches
+    through `sampler`, count how many batches need each node as an input node, return (rank_nodes, rank_freq)
+    as int32 CUDA tensors (frequency descending, ties by node id descending)."""
+    freq = torch.zeros(num_node, dtype=torch.int32, device=sampler.device)
+    for i, seeds in enumerate(batches):
+        mb = sampler.sample(seeds, batch_key=key0 + i)
+        nodes = mb.input_nodes
+        check(lib.xg_presample_accumulate(_ptr(freq), num_node, _ptr(nodes), nodes.numel(), None, _stream()))
+        torch.cuda.current_stream().synchronize()  # the slot is recycled on release
+        mb.release()
+    rank_nodes = torch.empty(num_node, dtype=torch.int32, device=sampler.device)
+    rank_freq = torch.empty(num_node, dtype=torch.int32, device=sampler.device)
+    check(lib.xg_presample_rank(_ptr(freq), num_node, _ptr(rank_nodes), _ptr(rank_freq), _stream()))
+    return rank_nodes, rank_freq
+
+
 def predict_num_nodes(batch_size: int, fanout) -> int:
     arr = (c_uint32 * len(fanout))(*[int(f) for f in fanout])
     return int(lib.xg_predict_num_nodes(batch_size, arr, len(fanout)))
