@@ -19,6 +19,8 @@
 // Edge order: node-major in input order, slot-minor (cuda_sampling_khop0.cu:192-239 semantics).
 // Remote lists (peer HBM over NVLink, pinned host over PCIe) are read with plain loads through the
 // pointers in the by-value xg_graph handle.
+#include <cstdlib>
+
 #include "sampling.cuh"
 
 namespace xg {
@@ -235,7 +237,11 @@ int launch_variant(const xg_graph &g, const uint32_t *d_input, size_t num_input_
                    const SampleFusion &fusion, const ScanSpace &scan, cudaStream_t s) {
   const size_t tiles = (num_input_max + kSampleTile - 1) / kSampleTile;
   const unsigned grid = grid_for(tiles, 6);
-  const bool pipe = VPL == 1 && tiles <= (size_t)kNumSM * 6;
+  static const int force_pipe = [] {
+    const char *e = std::getenv("XG_SAMPLE_PIPE");  // experiment knob: 1 = always pipelined, 0 = never
+    return e ? std::atoi(e) : -1;
+  }();
+  const bool pipe = VPL == 1 && (force_pipe >= 0 ? force_pipe == 1 : tiles <= (size_t)kNumSM * 6);
 #define XG_LAUNCH_SAMPLE(F, P)                                                                              \
   sample_uniform_kernel<G, VPL, F, P><<<grid, kSampleBlock, 0, s>>>(                                        \
       g, d_input, (uint32_t)num_input_max, d_num_input, (uint32_t)fanout, d_out_src, d_out_dst, d_num_out, \
