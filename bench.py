@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-steps", type=int, default=20, help="steps of the per-stage CUDA-event pass")
+    ap.add_argument("--in-flight", type=int, default=2,
+                    help="minibatches queued ahead of the consumer (one being sampled + the extract phase of the one before)")
     ap.add_argument("--replicate", type=float, default=float(os.environ.get("XG_BENCH_REPLICATE", "0.6")),
                     help="N > 1 only: fraction of the nodes (hottest first, by degree rank) whose feature rows every GPU "
                          "keeps in its own HBM; the rest is sharded rank %% P (0 = the reference's pure sharding)")
@@ -368,7 +370,7 @@ def run_xgnn(args):
 
     stream = torch.cuda.Stream(priority=-1)  # sample phase: short latency-bound kernels, scheduled first
     sm = ops.MinibatchSampler(st.graph, FANOUT, args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
-                              label=st.label, seed=2024, num_slots=3, device=local, stream=stream)
+                              label=st.label, seed=2024, num_slots=args.in_flight + 1, device=local, stream=stream)
     total = args.warmup + args.steps
     batches = seed_batches(st.train, rank, world, args.batch, total)
     flat = np.concatenate(batches)
@@ -382,13 +384,13 @@ def run_xgnn(args):
         torch.cuda.synchronize()
 
     def run(first, count, src, on_dev):
-        """submit `count` minibatches, two in flight; returns (edges, input nodes)"""
+        """submit `count` minibatches, `--in-flight` of them queued ahead; returns (edges, input nodes)"""
         edges = rows = 0
         pend = []
         for i in range(first, first + count):
             s = src[offs[i]:offs[i + 1]]
             pend.append(sm.submit(s, batch_key=i))
-            if len(pend) == 2:
+            if len(pend) == args.in_flight:
                 mb = sm.wait(pend.pop(0))
                 edges += sum(mb.num_edge); rows += mb.num_input
                 mb.release()
@@ -539,7 +541,7 @@ def main():
         "dtype": "u32", "data": "synthetic", "config": workload_config(args, st.num_node, R["num_edge"], world),
         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": args.batch * 4 + 24, "d2h_bytes_per_step": 120,
                 "ms_per_step": 1e3 * R["e2e_s"] / args.steps,
-                "note": "host seeds -> xg_sampler_submit (H2D inside) -> xg_batch_wait (D2H counts); two batches in flight"},
+                "note": f"host seeds -> xg_sampler_submit (H2D inside) -> xg_batch_wait (D2H counts); {args.in_flight} batches in flight"},
         "gpu_launches": int(R["launches"]),
         "clocks": R["clk"],
         "roofline": {"bound": bound, "kernel": top, "achieved": round(achieved, 1), "peak": peak_used, "unit": "GB/s",

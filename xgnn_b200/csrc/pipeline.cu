@@ -64,6 +64,7 @@ size_t elem_bytes(int dtype) {
 struct xg_batch {
   xg_sampler *owner = nullptr;
   int index = 0;
+  int lane = 0;  // which sample lane (hash table + scratch + stream) this slot's graph was captured on
   std::atomic<int> claimed{0};
   // device
   uint32_t *seeds = nullptr, *seed_local = nullptr, *input_nodes = nullptr;
@@ -100,37 +101,45 @@ struct xg_sampler {
   size_t cap_edge[XG_MAX_LAYERS] = {};  // most sampled edges of layer l
   size_t cap_input = 0;                 // most input_nodes of a batch
   size_t row_bytes = 0;
-  xg_hashtable *table = nullptr;
-  TableView view{};
-  uint32_t *dst_global = nullptr, *pos = nullptr;  // per-layer scratch, reused layer after layer
-  void *scan_mem = nullptr;
+  // A sample LANE = one hash table + per-layer scratch + one stream.  Batches of one lane are strictly ordered;
+  // a second lane (XG_SAMPLE_LANES=2) lets the sample phases of two consecutive batches run side by side.
+  struct Lane {
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    xg_hashtable *table = nullptr;
+    TableView view{};
+    uint32_t *dst_global = nullptr, *pos = nullptr;  // per-layer scratch, reused layer after layer
+    void *scan_mem = nullptr;
+    ExtWorkspace ext;  // scratch of the with-replacement / weighted samplers
+    std::atomic<bool> dirty{false};  // a batch overflowed: unnumbered keys may be left in the table
+  };
+  Lane lanes[2];
+  int num_lanes = 1;
+  int next_lane = 0;
   size_t scan_bytes = 0, scan_tiles_a = 0, scan_tiles_b = 0;
-  cudaStream_t stream = nullptr;    // sample phase: shares the hash table and the per-layer scratch -> strictly ordered
+  cudaStream_t stream = nullptr;    // == lanes[0].stream (sample phase of lane 0)
   cudaStream_t xstream = nullptr;   // extract phase: touches only the batch slot's own buffers (== stream in 1-stream mode)
-  bool own_stream = false;
   bool two_streams = false;
   bool timeline = false;            // XG_TIMELINE=1: timed events around both phases of every batch
   cudaEvent_t origin = nullptr;
   bool use_graph = true;
   bool stage_timing = false;
   bool uniform = true;      // KHop0/2/3: fused sample + insert kernel
-  ExtWorkspace ext;         // scratch of the with-replacement / weighted samplers
   WeightTables weights;
   uint32_t launches_per_batch = 0;
   uint32_t launches_phase[2] = {0, 0};
   std::mutex mu;
   std::vector<xg_batch *> slots;
-  std::atomic<bool> dirty{false};  // a batch overflowed: unnumbered keys may be left in the table
 };
 
 namespace {
 
-ScanSpace scan_a(xg_sampler *s) {
-  auto *w = reinterpret_cast<uint64_t *>(s->scan_mem);
+ScanSpace scan_a(xg_sampler *s, xg_sampler::Lane &ln) {
+  auto *w = reinterpret_cast<uint64_t *>(ln.scan_mem);
   return ScanSpace{reinterpret_cast<uint32_t *>(w), w + 1, s->scan_tiles_a};
 }
-ScanSpace scan_b(xg_sampler *s) {
-  auto *w = reinterpret_cast<uint64_t *>(s->scan_mem) + 1 + s->scan_tiles_a;
+ScanSpace scan_b(xg_sampler *s, xg_sampler::Lane &ln) {
+  auto *w = reinterpret_cast<uint64_t *>(ln.scan_mem) + 1 + s->scan_tiles_a;
   return ScanSpace{reinterpret_cast<uint32_t *>(w), w + 1, s->scan_tiles_b};
 }
 
@@ -200,18 +209,19 @@ void free_slot(xg_batch *b) {
 }
 
 // The Task in two stream-ordered phases; no host synchronisation, no allocation (capturable).
-//   sample phase  (s->stream):  Reset .. collect_counts: uses the sampler-wide hash table and scratch
+//   sample phase  (lane stream): Reset .. collect_counts: uses the lane's hash table and scratch
 //   extract phase (s->xstream): feature + label gather and the one D2H: reads only slot-owned buffers
 // so the extract phase of batch i (HBM/NVLink-bandwidth bound) runs while batch i+1 is being sampled
 // (latency bound, ~20 % of DRAM bandwidth).
 int enqueue_sample(xg_sampler *s, xg_batch *b) {
-  cudaStream_t st = s->stream;
+  xg_sampler::Lane &ln = s->lanes[b->lane];
+  cudaStream_t st = ln.stream;
   const int L = (int)s->cfg.num_layer;
   const size_t B = s->cfg.batch_size;
   // the table's unique list (n2o) IS this slot's input_nodes buffer: the numbering kernels append straight into
   // it, so task->input_nodes needs no copy and the next batch (another slot) cannot overwrite it while the
   // extract phase of this one is still reading
-  TableView t = s->view;
+  TableView t = ln.view;
   t.n2o = b->input_nodes;
   t.n2o_cap = (uint32_t)s->cap_input;
   const uint64_t *d_nseed64 = &b->d_params->num_seeds;
@@ -226,16 +236,16 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
   int rc = launch_table_clear(t, L + 1, s->cap_input, st);
   if (rc) return rc;
   // FillWithDupRevised(output_nodes) (dist_loops.cc:106-107)
-  XG_CUDA(cudaMemsetAsync(s->scan_mem, 0, s->scan_bytes, st));
-  if ((rc = launch_table_insert(t, b->seeds, s->pos, B, d_nseed64, st))) return rc;
-  if ((rc = launch_table_assign(t, s->pos, B, d_nseed64, 1, scan_b(s), st))) return rc;
-  if ((rc = launch_table_gather_local(t, s->pos, b->seed_local, B, d_nseed64, st))) return rc;
+  XG_CUDA(cudaMemsetAsync(ln.scan_mem, 0, s->scan_bytes, st));
+  if ((rc = launch_table_insert(t, b->seeds, ln.pos, B, d_nseed64, st))) return rc;
+  if ((rc = launch_table_assign(t, ln.pos, B, d_nseed64, 1, scan_b(s, ln), st))) return rc;
+  if ((rc = launch_table_gather_local(t, ln.pos, b->seed_local, B, d_nseed64, st))) return rc;
   mark();
 
   for (int l = L - 1; l >= 0; --l) {  // seeds outward (dist_loops.cc:120-123)
     const int fill = (L - 1 - l) + 2;
     const bool seed_layer = (l == L - 1);
-    XG_CUDA(cudaMemsetAsync(s->scan_mem, 0, s->scan_bytes, st));
+    XG_CUDA(cudaMemsetAsync(ln.scan_mem, 0, s->scan_bytes, st));
     uint64_t *d_num_edge = &b->d_counts->num_edge[l];
     const uint32_t *in_nodes = seed_layer ? b->seeds : t.n2o;
     const uint32_t *d_num_in = seed_layer ? d_nseed32 : &t.items[fill - 1];
@@ -245,34 +255,34 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
     if (s->uniform) {
       SampleFusion fusion{};
       fusion.table = t;
-      fusion.pos_out = s->pos;
+      fusion.pos_out = ln.pos;
       fusion.src_local = src_local;
       fusion.csc_indptr = b->csc_indptr[l];
       fusion.enabled = true;
-      rc = launch_sample_uniform(s->graph, in_nodes, s->cap_in[l], d_num_in, s->cfg.fanout[l], b->col[l], s->dst_global,
-                                 d_num_edge, 0, 0, &b->d_params->rng_key, salt, fusion, scan_a(s), st);
+      rc = launch_sample_uniform(s->graph, in_nodes, s->cap_in[l], d_num_in, s->cfg.fanout[l], b->col[l], ln.dst_global,
+                                 d_num_edge, 0, 0, &b->d_params->rng_key, salt, fusion, scan_a(s, ln), st);
       if (rc) return rc;
     } else {
       if (s->cfg.sample_type == XG_RANDOM_WALK) {
         rc = launch_random_walk(s->graph, in_nodes, s->cap_in[l], d_num_in, s->cfg.random_walk_length,
                                 s->cfg.random_walk_restart_prob, s->cfg.num_random_walk, s->cfg.fanout[l], true,
-                                src_local, b->col[l], s->dst_global, b->data[l], d_num_edge, make_uint2(0, 0),
-                                &b->d_params->rng_key, salt, scan_a(s), st);
+                                src_local, b->col[l], ln.dst_global, b->data[l], d_num_edge, make_uint2(0, 0),
+                                &b->d_params->rng_key, salt, scan_a(s, ln), st);
       } else {
         rc = launch_sample_ext(s->cfg.sample_type, s->graph, s->weights, in_nodes, s->cap_in[l], d_num_in,
-                               s->cfg.fanout[l], true, src_local, b->col[l], s->dst_global, d_num_edge,
-                               make_uint2(0, 0), &b->d_params->rng_key, salt, s->ext, st);
+                               s->cfg.fanout[l], true, src_local, b->col[l], ln.dst_global, d_num_edge,
+                               make_uint2(0, 0), &b->d_params->rng_key, salt, ln.ext, st);
       }
       if (rc) return rc;
       // unfused: the neighbours go into the table in a pass of their own
-      if ((rc = launch_table_insert(t, s->dst_global, s->pos, s->cap_edge[l], d_num_edge, st))) return rc;
+      if ((rc = launch_table_insert(t, ln.dst_global, ln.pos, s->cap_edge[l], d_num_edge, st))) return rc;
     }
     mark();
     // FillWithDuplicates(out_dst) + GPUMapEdges (dist_loops.cc:279-297): number the new ids, then
     // one 8-byte load per edge at the remembered slot gives the neighbour's local id
-    if ((rc = launch_table_assign(t, s->pos, s->cap_edge[l], d_num_edge, fill, scan_b(s), st))) return rc;
+    if ((rc = launch_table_assign(t, ln.pos, s->cap_edge[l], d_num_edge, fill, scan_b(s, ln), st))) return rc;
     mark();
-    if ((rc = launch_table_gather_local(t, s->pos, b->row[l], s->cap_edge[l], d_num_edge, st))) return rc;
+    if ((rc = launch_table_gather_local(t, ln.pos, b->row[l], s->cap_edge[l], d_num_edge, st))) return rc;
     mark();
   }
 
@@ -401,35 +411,16 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
   s->scan_tiles_b = tiles_b + 1;
   s->scan_bytes = (2 + s->scan_tiles_a + s->scan_tiles_b) * sizeof(uint64_t);
 
-  int rc = xg_hashtable_create(&s->table, s->cap_input, device);
-  if (rc) {
-    delete s;
-    return rc;
-  }
-  s->view = table_view(s->table);
-  XG_CUDA(cudaMalloc(&s->dst_global, max_edge * sizeof(uint32_t)));
-  XG_CUDA(cudaMalloc(&s->pos, max_edge * sizeof(uint32_t)));
-  XG_CUDA(cudaMalloc(&s->scan_mem, s->scan_bytes));
-  if (!uniform && cfg->sample_type != XG_RANDOM_WALK) {
-    size_t max_in = 1, max_f = 1;
-    for (int l = 0; l < L; ++l) {
-      if (s->cap_in[l] > max_in) max_in = s->cap_in[l];
-      if (cfg->fanout[l] > max_f) max_f = cfg->fanout[l];
-    }
-    // cap_slots must cover the largest layer: reserve by the largest product
-    size_t max_slots = 1;
-    for (int l = 0; l < L; ++l) max_slots = std::max(max_slots, s->cap_edge[l]);
-    if ((rc = ext_reserve(s->ext, max_in, (max_slots + max_in - 1) / max_in, nullptr))) {
-      xg_sampler_destroy(s);
-      return rc;
-    }
-    (void)max_f;
-  }
   const char *env = std::getenv("XG_NO_GRAPH");
   s->stage_timing = (cfg->flags & XG_SAMPLER_STAGE_TIMING) != 0;
   s->use_graph = !(cfg->flags & (XG_SAMPLER_NO_GRAPH | XG_SAMPLER_STAGE_TIMING)) && !(env && env[0] == '1');
   const char *one = std::getenv("XG_SINGLE_STREAM");
   s->two_streams = !s->stage_timing && !(cfg->flags & XG_SAMPLER_SINGLE_STREAM) && !(one && one[0] == '1');
+  // one lane by default: measured on B200 (profiles/r01h_sweep_lanes.txt) a second lane does not help - with the
+  // extract phase already running beside it the memory system is the shared limit (1.30 ms/minibatch with one lane,
+  // 1.34 with two); XG_SAMPLE_LANES=2 keeps the experiment reproducible
+  s->num_lanes = 1;
+  if (const char *nl = std::getenv("XG_SAMPLE_LANES")) s->num_lanes = (s->two_streams && std::atoi(nl) >= 2) ? 2 : 1;
   if (const char *fg = std::getenv("XG_L2_FETCH")) {  // experiment knob: 32 / 64 / 128-byte L2 fetch granularity
     cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)std::atoi(fg));
   }
@@ -437,13 +428,37 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
   s->timeline = tl && tl[0] == '1';
   int prio_low = 0, prio_high = 0;
   XG_CUDA(cudaDeviceGetStreamPriorityRange(&prio_low, &prio_high));
-  if (cfg->stream) {
-    s->stream = as_stream(cfg->stream);
-  } else {
-    // the sample phase is a chain of short latency-bound kernels: let its CTAs go first
-    XG_CUDA(cudaStreamCreateWithPriority(&s->stream, cudaStreamNonBlocking, prio_high));
-    s->own_stream = true;
+  int rc = XG_OK;
+  for (int k = 0; k < s->num_lanes; ++k) {
+    xg_sampler::Lane &ln = s->lanes[k];
+    if ((rc = xg_hashtable_create(&ln.table, s->cap_input, device))) {
+      xg_sampler_destroy(s);
+      return rc;
+    }
+    ln.view = table_view(ln.table);
+    XG_CUDA(cudaMalloc(&ln.dst_global, max_edge * sizeof(uint32_t)));
+    XG_CUDA(cudaMalloc(&ln.pos, max_edge * sizeof(uint32_t)));
+    XG_CUDA(cudaMalloc(&ln.scan_mem, s->scan_bytes));
+    if (!uniform && cfg->sample_type != XG_RANDOM_WALK) {
+      size_t max_in = 1;
+      for (int l = 0; l < L; ++l) max_in = std::max(max_in, s->cap_in[l]);
+      // cap_slots must cover the largest layer: reserve by the largest product
+      size_t max_slots = 1;
+      for (int l = 0; l < L; ++l) max_slots = std::max(max_slots, s->cap_edge[l]);
+      if ((rc = ext_reserve(ln.ext, max_in, (max_slots + max_in - 1) / max_in, nullptr))) {
+        xg_sampler_destroy(s);
+        return rc;
+      }
+    }
+    if (k == 0 && cfg->stream) {
+      ln.stream = as_stream(cfg->stream);
+    } else {
+      // the sample phase is a chain of short latency-bound kernels: let its CTAs go first
+      XG_CUDA(cudaStreamCreateWithPriority(&ln.stream, cudaStreamNonBlocking, prio_high));
+      ln.own_stream = true;
+    }
   }
+  s->stream = s->lanes[0].stream;
   if (s->two_streams) XG_CUDA(cudaStreamCreateWithPriority(&s->xstream, cudaStreamNonBlocking, prio_low));
   else s->xstream = s->stream;
   if (s->timeline) {
@@ -458,6 +473,7 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
       return rc;
     }
     b->index = (int)i;
+    b->lane = (int)(i % (uint32_t)s->num_lanes);
     s->slots.push_back(b);
   }
   *out = s;
@@ -467,16 +483,20 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
 int xg_sampler_destroy(xg_sampler *s) {
   if (!s) return XG_OK;
   DeviceScope scope(s->device);
-  if (s->stream) cudaStreamSynchronize(s->stream);
+  for (int k = 0; k < 2; ++k)
+    if (s->lanes[k].stream) cudaStreamSynchronize(s->lanes[k].stream);
   if (s->two_streams && s->xstream) cudaStreamSynchronize(s->xstream);
   for (auto *b : s->slots) free_slot(b);
-  cudaFree(s->dst_global);
-  cudaFree(s->pos);
-  cudaFree(s->scan_mem);
-  ext_release(s->ext);
-  if (s->table) xg_hashtable_destroy(s->table);
+  for (int k = 0; k < 2; ++k) {
+    xg_sampler::Lane &ln = s->lanes[k];
+    cudaFree(ln.dst_global);
+    cudaFree(ln.pos);
+    cudaFree(ln.scan_mem);
+    ext_release(ln.ext);
+    if (ln.table) xg_hashtable_destroy(ln.table);
+    if (ln.own_stream && ln.stream) cudaStreamDestroy(ln.stream);
+  }
   if (s->origin) cudaEventDestroy(s->origin);
-  if (s->own_stream && s->stream) cudaStreamDestroy(s->stream);
   if (s->two_streams && s->xstream) cudaStreamDestroy(s->xstream);
   delete s;
   return XG_OK;
@@ -490,28 +510,34 @@ int xg_sampler_submit(xg_sampler *s, const uint32_t *seeds, size_t num_seeds, in
   DeviceScope scope(s->device);
   std::lock_guard<std::mutex> lk(s->mu);
   xg_batch *b = nullptr;
-  for (auto *c : s->slots) {
-    int expected = 0;
-    if (c->claimed.compare_exchange_strong(expected, 1)) {
-      b = c;
-      break;
+  // alternate the sample lanes: first look for a free slot on the lane whose turn it is, then on any lane
+  for (int pass = 0; pass < 2 && !b; ++pass) {
+    for (auto *c : s->slots) {
+      if (pass == 0 && c->lane != s->next_lane) continue;
+      int expected = 0;
+      if (c->claimed.compare_exchange_strong(expected, 1)) {
+        b = c;
+        break;
+      }
     }
   }
   if (!b) {
     set_error("every batch slot is still held: release a batch (xg_batch_release) or raise num_slots");
     return XG_ERR_CAPACITY;
   }
-  cudaStream_t st = s->stream;
+  s->next_lane = (b->lane + 1) % s->num_lanes;
+  xg_sampler::Lane &ln = s->lanes[b->lane];
+  cudaStream_t st = ln.stream;
   // the slot's pinned staging is about to be rewritten: its previous batch must have drained
   if (b->recorded && cudaEventSynchronize(b->done) != cudaSuccess) {
     b->claimed.store(0);
     set_error("cudaEventSynchronize failed on a recycled batch slot");
     return XG_ERR_CUDA;
   }
-  if (s->dirty.exchange(false)) {  // after an overflow the targeted Reset cannot know every used slot
-    const size_t cap = (size_t)s->view.cap;
-    if (cudaMemsetAsync(s->view.slots, 0xFF, cap * sizeof(uint2), st) != cudaSuccess ||
-        cudaMemsetAsync(s->view.items, 0, (kMaxFills + 2) * sizeof(uint32_t), st) != cudaSuccess) {
+  if (ln.dirty.exchange(false)) {  // after an overflow the targeted Reset cannot know every used slot
+    const size_t cap = (size_t)ln.view.cap;
+    if (cudaMemsetAsync(ln.view.slots, 0xFF, cap * sizeof(uint2), st) != cudaSuccess ||
+        cudaMemsetAsync(ln.view.items, 0, (kMaxFills + 2) * sizeof(uint32_t), st) != cudaSuccess) {
       b->claimed.store(0);
       return XG_ERR_CUDA;
     }
@@ -612,7 +638,7 @@ int xg_batch_wait(xg_batch *b, xg_batch_view *view) {
   }
   if (c.items[L + 1] > s->cap_input) over = true;
   if (over) {
-    s->dirty.store(true);
+    s->lanes[b->lane].dirty.store(true);
     set_error("minibatch outgrew its buffers (max_input_nodes=" + std::to_string(s->cap_input) + ")");
     return XG_ERR_CAPACITY;
   }
