@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-steps", type=int, default=20, help="steps of the per-stage CUDA-event pass")
+    ap.add_argument("--max-input-nodes", type=int, default=0,
+                    help="cap on a minibatch's unique nodes (sizes the hash table and the batch buffers); 0 = worst case "
+                         "PredictNumNodes (common.cc:488-497)")
     ap.add_argument("--in-flight", type=int, default=2,
                     help="minibatches queued ahead of the consumer (one being sampled + the extract phase of the one before)")
     ap.add_argument("--replicate", type=float, default=float(os.environ.get("XG_BENCH_REPLICATE", "0.6")),
@@ -370,7 +373,8 @@ def run_xgnn(args):
 
     stream = torch.cuda.Stream(priority=-1)  # sample phase: short latency-bound kernels, scheduled first
     sm = ops.MinibatchSampler(st.graph, FANOUT, args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
-                              label=st.label, seed=2024, num_slots=args.in_flight + 1, device=local, stream=stream)
+                              label=st.label, seed=2024, num_slots=args.in_flight + 1, device=local, stream=stream,
+                              max_input_nodes=args.max_input_nodes)
     total = args.warmup + args.steps
     batches = seed_batches(st.train, rank, world, args.batch, total)
     flat = np.concatenate(batches)
@@ -455,7 +459,7 @@ def stage_pass(R, args):
     torch, st = R["torch"], R["st"]
     sm2 = ops.MinibatchSampler(st.graph, FANOUT, args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
                                label=st.label, seed=2024, num_slots=1, device=R["local"], stream=R["stream"],
-                               use_graph=False, stage_timing=True)
+                               use_graph=False, stage_timing=True, max_input_nodes=args.max_input_nodes)
     L = len(FANOUT)
     acc = {}
     info = {"edges": [0] * L, "inputs": [0] * L, "rows": 0, "seeds": 0, "src_local": 0, "src_peer": 0, "src_host": 0}
