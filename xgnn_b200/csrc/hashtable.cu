@@ -55,7 +55,8 @@ table_fill_unique_kernel(TableView t, const uint32_t *__restrict__ keys, size_t 
 // Tiles are handed out by a ticket so that the chained scan's ordering requirement holds for any
 // grid size.
 __global__ void __launch_bounds__(kAssignBlock)
-table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, size_t n_max, const uint64_t *d_n,
+table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, uint32_t *__restrict__ local_out, size_t n_max,
+                    const uint64_t *d_n,
                     int fill, uint32_t *ticket, uint64_t *scan_state) {
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_cnt[kAssignItems * (kAssignBlock / 32)];
@@ -129,10 +130,32 @@ table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, size_t n_max,
           t.n2o_slot[local] = slot_pos[k];
         } else {
           *t.overflow = 1;
+          t.slots[slot_pos[k]].y = kPosTag - 1;  // numbered "out of range": releases the waiters below; the batch is discarded
         }
+        slot[k].y = local;
       }
     }
-    __syncthreads();  // s_tile / s_cnt are reused by the next tile
+    __syncthreads();  // s_tile / s_cnt are reused by the next tile; this tile's local ids are visible CTA-wide
+    if (local_out != nullptr) {
+      // Fused remap (GPUMapEdges for the dst side): every position gets the local id of its key in the same pass.
+      // A later occurrence whose slot still holds a tagged position waits for the FIRST occurrence to be numbered:
+      // that one sits at a smaller position, i.e. in this tile (already written, see the barrier above) or in a tile
+      // with a smaller ticket, which is running or done and never waits on a later tile - so the wait terminates.
+#pragma unroll
+      for (int k = 0; k < kAssignItems; ++k) {
+        const uint64_t e = tile_base + (uint64_t)k * kAssignBlock + threadIdx.x;
+        if (e >= n) continue;
+        uint32_t v = kEmpty;
+        if (slot_pos[k] != kEmpty) {
+          v = slot[k].y;
+          if (v >= kPosTag) {
+            const volatile uint32_t *vp = &t.slots[slot_pos[k]].y;
+            while ((v = *vp) >= kPosTag) __nanosleep(20);
+          }
+        }
+        local_out[e] = v;
+      }
+    }
   }
 }
 
@@ -192,10 +215,10 @@ int launch_table_insert(const TableView &t, const uint32_t *keys, uint32_t *pos_
 }
 
 int launch_table_assign(const TableView &t, const uint32_t *pos, size_t n_max, const uint64_t *d_n,
-                        int fill, const ScanSpace &scan, cudaStream_t s) {
+                        int fill, const ScanSpace &scan, cudaStream_t s, uint32_t *local_out) {
   size_t tiles = (n_max + kAssignTile - 1) / kAssignTile;
   XG_REQUIRE(tiles <= scan.max_tiles, "scan workspace too small");
-  table_assign_kernel<<<grid_for(tiles, 8), kAssignBlock, 0, s>>>(t, pos, n_max, d_n, fill, scan.ticket,
+  table_assign_kernel<<<grid_for(tiles, 8), kAssignBlock, 0, s>>>(t, pos, local_out, n_max, d_n, fill, scan.ticket,
                                                                   scan.state);
   XG_LAUNCHED();
   return XG_OK;

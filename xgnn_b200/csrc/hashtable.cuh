@@ -113,8 +113,9 @@ constexpr int kAssignTile = kAssignBlock * kAssignItems;
 int launch_table_insert(const TableView &t, const uint32_t *keys, uint32_t *pos_out, size_t n_max,
                         const uint64_t *d_n, cudaStream_t s);
 // number the first occurrences: items[fill] = items[fill-1] + #new; n2o appended; slot.val = local
+// local_out != NULL: also write local_out[i] = local id of the key at position i (the remap, fused: no second pass)
 int launch_table_assign(const TableView &t, const uint32_t *pos, size_t n_max, const uint64_t *d_n,
-                        int fill, const ScanSpace &scan, cudaStream_t s);
+                        int fill, const ScanSpace &scan, cudaStream_t s, uint32_t *local_out = nullptr);
 // Reset in O(items): slots[n2o_slot[i]] = free for i < items[fill], then items[] = 0 (stream-ordered)
 int launch_table_clear(const TableView &t, int fill, size_t max_items, cudaStream_t s);
 // out[i] = slots[pos[i]].val

@@ -238,8 +238,7 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
   // FillWithDupRevised(output_nodes) (dist_loops.cc:106-107)
   XG_CUDA(cudaMemsetAsync(ln.scan_mem, 0, s->scan_bytes, st));
   if ((rc = launch_table_insert(t, b->seeds, ln.pos, B, d_nseed64, st))) return rc;
-  if ((rc = launch_table_assign(t, ln.pos, B, d_nseed64, 1, scan_b(s, ln), st))) return rc;
-  if ((rc = launch_table_gather_local(t, ln.pos, b->seed_local, B, d_nseed64, st))) return rc;
+  if ((rc = launch_table_assign(t, ln.pos, B, d_nseed64, 1, scan_b(s, ln), st, b->seed_local))) return rc;
   mark();
 
   for (int l = L - 1; l >= 0; --l) {  // seeds outward (dist_loops.cc:120-123)
@@ -280,10 +279,10 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
     mark();
     // FillWithDuplicates(out_dst) + GPUMapEdges (dist_loops.cc:279-297): number the new ids, then
     // one 8-byte load per edge at the remembered slot gives the neighbour's local id
-    if ((rc = launch_table_assign(t, ln.pos, s->cap_edge[l], d_num_edge, fill, scan_b(s, ln), st))) return rc;
+    // ... and the neighbour's local id for every edge in the same pass (no second walk over the table)
+    if ((rc = launch_table_assign(t, ln.pos, s->cap_edge[l], d_num_edge, fill, scan_b(s, ln), st, b->row[l]))) return rc;
     mark();
-    if ((rc = launch_table_gather_local(t, ln.pos, b->row[l], s->cap_edge[l], d_num_edge, st))) return rc;
-    mark();
+    mark();  // (the separate remap stage of earlier revisions: fused above, kept as an empty stage for the timing ABI)
   }
 
   // task->input_nodes = the unique list (dist_loops.cc:357), already in place; counts leave the table before the next Reset
