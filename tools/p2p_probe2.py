@@ -64,6 +64,12 @@ def main():
     # mixed but warp-segregated: 32-row groups are all-local or all-remote
     grp = (torch.arange(N, device="cuda") // 32) % 2
     idx_seg = torch.where(grp == 0, idx_local, idx_remote)
+    # 20 % of the rows on the peer (the two-tier store's regime): mixed at random, grouped per warp, fully sorted
+    pick = torch.rand(N, device="cuda", generator=g) < 0.2
+    idx_mix20 = torch.where(pick, idx_remote, idx_local)
+    grp5 = (torch.arange(N, device="cuda") // 32) % 5 == 0
+    idx_seg20 = torch.where(grp5, idx_remote, idx_local)
+    idx_sort20 = torch.cat([idx_local[: int(N * 0.8)], idx_remote[: N - int(N * 0.8)]])
     st = torch.cuda.current_stream().cuda_stream
 
     def gather(idx):
@@ -93,7 +99,10 @@ def main():
              ("mixed 50/50, rank0 alone", idx_mixed, (0,)),
              ("mixed 50/50, both ranks", idx_mixed, (0, 1)),
              ("warp-segregated 50/50, rank0 alone", idx_seg, (0,)),
-             ("warp-segregated 50/50, both ranks", idx_seg, (0, 1))]
+             ("warp-segregated 50/50, both ranks", idx_seg, (0, 1)),
+             ("20 % peer, mixed, both ranks", idx_mix20, (0, 1)),
+             ("20 % peer, warp-segregated, both ranks", idx_seg20, (0, 1)),
+             ("20 % peer, local rows first then peer rows, both ranks", idx_sort20, (0, 1))]
     for name, idx, active in cases:
         ms = timed(idx, active)
         t = torch.tensor([ms if ms is not None else 0.0], dtype=torch.float64, device="cuda")
