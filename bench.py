@@ -44,6 +44,9 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--stage-steps", type=int, default=20, help="steps of the per-stage CUDA-event pass")
+    ap.add_argument("--sample-type", type=int, default=0,
+                    help="SampleType numbering of common.h:50-59: 0 KHop0 (default), 1 KHop1, 3 random walk (W=4, len 3, "
+                         "restart 0.5, K=5: sgnn/train_pinsage.py:138-142), 7 KHop3; secondary workloads, not the headline")
     ap.add_argument("--max-input-nodes", type=int, default=0,
                     help="cap on a minibatch's unique nodes (sizes the hash table and the batch buffers); 0 = worst case "
                          "PredictNumNodes (common.cc:488-497)")
@@ -293,11 +296,14 @@ def placement_note(args, world, V, row_bytes):
 def workload_config(args, V, E, world):
     from xgnn_b200 import dataset as D
     dim, dtype = D.SHAPES[args.shape][2], str(D.SHAPES[args.shape][3]).replace("torch.float", "fp")
-    return {"workload": f"GraphSAGE 3-hop uniform fanout 15,10,5 on synthetic {args.shape}-shape graph "
+    kind = {0: "GraphSAGE 3-hop uniform fanout 15,10,5", 7: "GraphSAGE 3-hop uniform (KHop3) fanout 15,10,5",
+            1: "3-hop KHop1 (with replacement, sort + adjacent dedup) fanout 15,10,5",
+            3: "PinSAGE 3-layer random-walk top-K (4 walks x 3 steps, restart 0.5, K=5)"}.get(args.sample_type, "3-hop")
+    return {"workload": f"{kind} on synthetic {args.shape}-shape graph "
                         f"({V / 1e6:.1f}M nodes, {E / 1e9:.2f}B edges, {dim}-d {dtype}), batch {args.batch}, "
                         f"sample + unique/remap + feature/label extract per minibatch",
             "shape": args.shape, "scale": args.scale, "num_node": V, "num_edge": E, "batch": args.batch,
-            "fanout_from_seeds": FANOUT[::-1],
+            "fanout_from_seeds": fanout_of(args)[::-1], "sample_type": args.sample_type,
             "placement": placement_note(args, world, V, dim * (2 if "16" in dtype else 4)),
             "replicate": (args.replicate if world > 1 else 0.0),
             "l2": "inputs larger than L2 (store is GBs; fresh seeds every step)"}
@@ -372,9 +378,9 @@ def run_xgnn(args):
     t_build = time.perf_counter() - t_build
 
     stream = torch.cuda.Stream(priority=-1)  # sample phase: short latency-bound kernels, scheduled first
-    sm = ops.MinibatchSampler(st.graph, FANOUT, args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
+    sm = ops.MinibatchSampler(st.graph, fanout_of(args), args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
                               label=st.label, seed=2024, num_slots=args.in_flight + 1, device=local, stream=stream,
-                              max_input_nodes=args.max_input_nodes)
+                              max_input_nodes=args.max_input_nodes, **sampler_kw(args))
     total = args.warmup + args.steps
     batches = seed_batches(st.train, rank, world, args.batch, total)
     flat = np.concatenate(batches)
@@ -448,6 +454,17 @@ def run_xgnn(args):
                 offs=offs, stream=stream)
 
 
+def fanout_of(args):
+    return [5, 5, 5] if args.sample_type == 3 else FANOUT  # random walk: K neighbours per layer
+
+
+def sampler_kw(args):
+    kw = {"sample_type": args.sample_type}
+    if args.sample_type == 3:
+        kw.update(random_walk_length=3, num_random_walk=4, random_walk_restart_prob=0.5)
+    return kw
+
+
 STAGES = {"reset_seeds": 0, "sample": 1, "number": 2, "remap": 3, "input_nodes": 4, "feature": 5, "label": 6}
 
 
@@ -457,9 +474,10 @@ def stage_pass(R, args):
     from xgnn_b200 import ops
     from xgnn_b200._clib import check, lib
     torch, st = R["torch"], R["st"]
-    sm2 = ops.MinibatchSampler(st.graph, FANOUT, args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
+    sm2 = ops.MinibatchSampler(st.graph, fanout_of(args), args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
                                label=st.label, seed=2024, num_slots=1, device=R["local"], stream=R["stream"],
-                               use_graph=False, stage_timing=True, max_input_nodes=args.max_input_nodes)
+                               use_graph=False, stage_timing=True, max_input_nodes=args.max_input_nodes,
+                               **sampler_kw(args))
     L = len(FANOUT)
     acc = {}
     info = {"edges": [0] * L, "inputs": [0] * L, "rows": 0, "seeds": 0, "src_local": 0, "src_peer": 0, "src_host": 0}
