@@ -63,6 +63,13 @@ def check_minibatch_properties(mb, st, D, seeds_np, fanout, uniform=True):
             assert torch.equal(got, want)
             ip = _u32(mb.csc_indptr(l))  # CSC offsets == exclusive scan of the per-node counts
             assert int(ip[0]) == 0 and torch.equal(ip[1:] - ip[:-1], want)
+            # nodes with degree <= fanout keep their whole list in CSR order (the bit-exact branch): EVERY such edge's
+            # remapped neighbour must be the CSR entry at the same offset - checks sampler + unique + remap at scale
+            whole = deg[col] <= fanout[l]
+            off = torch.arange(col.numel(), device=dev) - ip[col]
+            src_global = nodes[col[whole]]
+            want_dst = _u32(st.local["indices"][indptr[src_global] + off[whole]])
+            assert torch.equal(inp[row[whole]], want_dst), "remapped neighbour differs from the CSR entry"
         # membership of a sample of edges in the CSR list of their source node
         g = torch.Generator(device="cpu").manual_seed(l)
         pick = torch.randint(0, row.numel(), (400,), generator=g).to(dev)
