@@ -410,6 +410,20 @@ def run_xgnn(args):
             mb.release()
         return edges, rows
 
+    # ---- self-check (untimed): one minibatch's rows against the generator's closed form, labels, prefix property -
+    mb = sm.wait(sm.submit(d_flat[offs[0]:offs[1]], batch_key=0))
+    want = D.gen_features(mb.num_input, st.dim, st.dtype, torch.device("cuda", local), row_ids=mb.input_nodes)
+    bits = torch.int32 if st.dtype == torch.float32 else torch.int16
+    ok = bool(torch.equal(mb.feat.view(bits), want.view(bits)))
+    ok = ok and bool(torch.equal(mb.input_nodes[: mb.num_output], d_flat[offs[0]:offs[1]]))
+    ok = ok and bool(torch.equal(mb.label, (d_flat[offs[0]:offs[1]].to(torch.int64) & 0xFFFFFFFF) % st.num_class))
+    del want
+    mb.release()
+    if dist is not None:
+        t_ok = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(t_ok, op=dist.ReduceOp.MIN)
+        ok = bool(t_ok.item())
+    assert ok, "self-check failed: gathered rows / labels / seed prefix differ from the generator"
     # ---- value: device-resident seeds, CUDA events on the sampler's stream ------------------------
     run(0, args.warmup, d_flat, True)
     clocks = ClockSampler(local)
@@ -574,6 +588,7 @@ def main():
                   "feature_gather_GBps": round(info["rows"] * row_bytes / stage_ms["feature"] / 1e6, 1),
                   "input_nodes_per_batch": info["rows"], "edges_per_batch": sum(info["edges"])},
         "build_s": round(R["t_build"], 1),
+        "self_check": "one minibatch per rank before timing: feature rows == generator closed form (0 ULP), labels, seed prefix",
     }
     if R["rank"] == 0 and world == 1 and not args.no_cpu_baseline:
         del R["sm"]
