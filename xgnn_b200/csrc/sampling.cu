@@ -236,12 +236,18 @@ int launch_variant(const xg_graph &g, const uint32_t *d_input, size_t num_input_
                    uint64_t *d_num_out, uint2 key, const uint2 *d_key, uint32_t salt,
                    const SampleFusion &fusion, const ScanSpace &scan, cudaStream_t s) {
   const size_t tiles = (num_input_max + kSampleTile - 1) / kSampleTile;
-  const unsigned grid = grid_for(tiles, 6);
+  static const int ctas_per_sm = [] {
+    // 8 x 256 threads = full occupancy at 32 registers; measured on B200 (0.9 M nodes -> 4.3 M edges): 4 CTAs/SM
+    // 0.316 ms, 6: 0.255, 8: 0.229, 12 (more tiles than residency): 0.229
+    const char *e = std::getenv("XG_SAMPLE_CTAS");
+    return e ? std::atoi(e) : 8;
+  }();
+  const unsigned grid = grid_for(tiles, ctas_per_sm);
   static const int force_pipe = [] {
     const char *e = std::getenv("XG_SAMPLE_PIPE");  // experiment knob: 1 = always pipelined, 0 = never
     return e ? std::atoi(e) : -1;
   }();
-  const bool pipe = VPL == 1 && (force_pipe >= 0 ? force_pipe == 1 : tiles <= (size_t)kNumSM * 6);
+  const bool pipe = VPL == 1 && (force_pipe >= 0 ? force_pipe == 1 : tiles <= (size_t)kNumSM * 6);  // one wave at the pipelined variant's residency
 #define XG_LAUNCH_SAMPLE(F, P)                                                                              \
   sample_uniform_kernel<G, VPL, F, P><<<grid, kSampleBlock, 0, s>>>(                                        \
       g, d_input, (uint32_t)num_input_max, d_num_input, (uint32_t)fanout, d_out_src, d_out_dst, d_num_out, \
