@@ -377,7 +377,8 @@ def run_xgnn(args):
         num_edge = st.local["num_local_edge"]
     t_build = time.perf_counter() - t_build
 
-    stream = torch.cuda.Stream(priority=-1)  # sample phase: short latency-bound kernels, scheduled first
+    # sample phase: short latency-bound kernels, scheduled first (XG_BENCH_SAMPLE_PRIO=0: default priority)
+    stream = torch.cuda.Stream(priority=int(os.environ.get("XG_BENCH_SAMPLE_PRIO", "-1")))
     sm = ops.MinibatchSampler(st.graph, fanout_of(args), args.batch, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
                               label=st.label, seed=2024, num_slots=args.in_flight + 1, device=local, stream=stream,
                               max_input_nodes=args.max_input_nodes, **sampler_kw(args))

@@ -458,7 +458,9 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
     }
   }
   s->stream = s->lanes[0].stream;
-  if (s->two_streams) XG_CUDA(cudaStreamCreateWithPriority(&s->xstream, cudaStreamNonBlocking, prio_low));
+  const char *xp = std::getenv("XG_EXTRACT_PRIO");  // experiment knob: "high" = extract phase first
+  if (s->two_streams)
+    XG_CUDA(cudaStreamCreateWithPriority(&s->xstream, cudaStreamNonBlocking, (xp && xp[0] == 'h') ? prio_high : prio_low));
   else s->xstream = s->stream;
   if (s->timeline) {
     XG_CUDA(cudaEventCreate(&s->origin));
