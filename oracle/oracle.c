@@ -8,7 +8,7 @@
  *
  * Pinning status (see DESIGN.md "Oracle"):
  *   - khop0 (deg <= fanout branch), hashtable0, map_edges, extract: pinned against the reference's
- *     own CPU code compiled in place (oracle/_ref/libxgnn_ref.so) by tests/test_oracle_vs_ref.py and
+ *     own CPU code compiled in place (oracle/_ref/libxgnn_ref.so) by tests/test_oracle.py (live) and
  *     against committed fixtures generated from it (tests/golden/*.npz).
  *   - hashtable properties: pinned against the reference's gtest vectors
  *     (samgraph/unittest/test_hashmap.cc:98-172).
