@@ -344,6 +344,15 @@ int xg_presample_accumulate(uint32_t *d_freq, uint32_t num_node, const uint32_t 
 int xg_presample_rank(const uint32_t *d_freq, uint32_t num_node, uint32_t *d_rank_nodes, uint32_t *d_rank_freq,
                       void *stream);
 
+/* SAMGRAPH_SANITY_CHECK: GPUBatchSanityCheck / GPUSanityCheckList (cuda/cuda_sanity_check.cu:28-88).  Violations are
+ * added to *d_violations (device u64) instead of asserting in the kernel.  ids: kEmptyKey, id >= num_node, or - when
+ * d_epoch_map (u32[num_node], zeroed at the start of an epoch) is given - an id already seen this epoch.
+ * edges: row[e] >= num_src or col[e] >= num_dst. */
+int xg_sanity_check_ids(const uint32_t *d_ids, size_t n, uint32_t num_node, uint32_t *d_epoch_map,
+                        uint64_t *d_violations, void *stream);
+int xg_sanity_check_edges(const uint32_t *d_row, const uint32_t *d_col, size_t n, uint32_t num_src, uint32_t num_dst,
+                          uint64_t *d_violations, void *stream);
+
 /* DistAlignedShuffler::ReShuffle, dist/dist_shuffler_aligned.cc:75-121: one epoch's Fisher-Yates pass with
  * std::default_random_engine(seed = epoch), in place over the padded train set (host memory).  The engine
  * applies it epoch after epoch to the same array, as the reference does. */

@@ -325,3 +325,33 @@ def test_extract_two_tier_store_vs_oracle(ops, P, pct, rep):
     local = hit & ((r < nrep) | (((r.astype(np.int64) - nrep) % P) == 0))
     st = stats.cpu().numpy()
     assert st[2] == (~hit).sum() and st[0] == local.sum() and st[1] == (hit & ~local).sum()
+
+
+def test_sanity_check_counts_violations():
+    """xg_sanity_check_ids / _edges count exactly the violations the reference's device asserts would trip on
+    (cuda/cuda_sanity_check.cu:28-88): kEmptyKey, ids out of range, ids repeated inside an epoch, edge endpoints outside
+    their block."""
+    from xgnn_b200 import ops
+    V = 1000
+    rng = np.random.default_rng(3)
+    ids = rng.permutation(V)[:600].astype(np.uint32)
+    d = torch.from_numpy(ids.view(np.int32)).cuda()
+    emap = torch.zeros(V, dtype=torch.int32, device="cuda")
+    assert ops.sanity_check_ids(d, V) == 0
+    assert ops.sanity_check_ids(d[:300], V, emap) == 0
+    assert ops.sanity_check_ids(d[300:], V, emap) == 0  # same epoch, disjoint batch
+    assert int(emap.sum()) == 600
+    assert ops.sanity_check_ids(d[100:150], V, emap) == 50  # 50 seeds seen twice in one epoch
+    bad = ids.copy()
+    bad[7] = 0xFFFFFFFF
+    bad[9] = V
+    bad[11] = bad[12]
+    db = torch.from_numpy(bad.view(np.int32)).cuda()
+    assert ops.sanity_check_ids(db, V) == 2
+    assert ops.sanity_check_ids(db, V, torch.zeros(V, dtype=torch.int32, device="cuda")) == 3
+    assert ops.sanity_check_ids(d[:0], V) == 0
+    row = torch.from_numpy(rng.integers(0, 50, 4000).astype(np.int32)).cuda()
+    col = torch.from_numpy(rng.integers(0, 20, 4000).astype(np.int32)).cuda()
+    assert ops.sanity_check_edges(row, col, 50, 20) == 0
+    want = int(((row >= 40) | (col >= 15)).sum())
+    assert ops.sanity_check_edges(row, col, 40, 15) == want and want > 0

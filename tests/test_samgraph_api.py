@@ -126,3 +126,12 @@ def test_presample_cache_policy_flows(dataset, mode, args):
     trainer builds its cache from that ranking; batches must still carry CPUExtract's rows bit for bit."""
     import torch
     _drive(mode, dataset, *args, env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "XG_TEST_PRESAMPLE": "1"})
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,args", [("single", (0,)), ("arch6", (0, 2))])
+def test_sanity_check_env_flows(dataset, mode, args):
+    """SAMGRAPH_SANITY_CHECK=1 (constant.cc:58; cuda_sanity_check.cu:28-88): every batch is checked on the device for
+    kEmptyKey, out-of-range ids / edge endpoints and seeds repeated inside an epoch; a clean run must pass untouched."""
+    import torch
+    _drive(mode, dataset, *args, env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "SAMGRAPH_SANITY_CHECK": "1"})

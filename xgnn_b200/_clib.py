@@ -156,6 +156,8 @@ _sig("xg_sampler_destroy", c_int, c_void_p)
 _sig("xg_sampler_submit", c_int, c_void_p, c_void_p, c_size_t, c_int, c_uint64, POINTER(c_void_p))
 _sig("xg_batch_wait", c_int, c_void_p, POINTER(XgBatchView))
 _sig("xg_batch_release", c_int, c_void_p)
+_sig("xg_sanity_check_ids", c_int, c_void_p, c_size_t, c_uint32, c_void_p, c_void_p, c_void_p)
+_sig("xg_sanity_check_edges", c_int, c_void_p, c_void_p, c_size_t, c_uint32, c_uint32, c_void_p, c_void_p)
 _sig("xg_presample_accumulate", c_int, c_void_p, c_uint32, c_void_p, c_size_t, c_void_p, c_void_p)
 _sig("xg_presample_rank", c_int, c_void_p, c_uint32, c_void_p, c_void_p, c_void_p)
 _sig("xg_sampler_stream", c_void_p, c_void_p)

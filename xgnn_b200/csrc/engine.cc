@@ -429,6 +429,11 @@ struct Engine {
   BatchPtr current;
   std::vector<std::thread> threads;
   bool producer_done = false;
+  // SAMGRAPH_SANITY_CHECK (constant.cc:58, run_config.cc option_sanity_check)
+  bool sanity_check = false;
+  uint64_t *d_sanity = nullptr;
+  uint32_t *d_epoch_map = nullptr;
+  size_t sanity_epoch = (size_t)-1;
 };
 Engine *g_engine = nullptr;
 
@@ -654,6 +659,7 @@ void create_sampler(Engine &e) {
   sc.feat_dtype = ds.feat_dtype;
   sc.seed = 0x58474E4Eull;  // reproducible, unlike the reference's wall-clock seed (cuda_random_states.cu:106-108)
   if (const char *s = std::getenv("SAMGRAPH_SEED")) sc.seed = std::strtoull(s, nullptr, 0);
+  if (const char *s = std::getenv("SAMGRAPH_SANITY_CHECK")) e.sanity_check = !std::strcmp(s, "ON") || !std::strcmp(s, "1");  // IsEnvSet, common.cc:517-525
   sc.stream = e.stream;
   sc.random_walk_length = (uint32_t)cfg.random_walk_length;
   sc.num_random_walk = (uint32_t)cfg.num_random_walk;
@@ -667,6 +673,35 @@ void create_sampler(Engine &e) {
 
 // RunSampleSubLoopOnce + RunCacheDataCopySubLoopOnce for one Task (dist_loops_arch6.cc:55-199).
 // Returns false once every epoch has been produced.
+// SAMGRAPH_SANITY_CHECK=1 (constant.cc:58; cuda_shuffler.cc:145-152 -> cuda_sanity_check.cu:28-88): every batch's seeds are
+// valid ids and - outside the aligned shuffler's wrap-around padding - unique within the epoch; every list is free of
+// kEmptyKey; every edge endpoint is inside its block.  A violation aborts like the reference's device assert.
+void sanity_check_batch(Engine &e, const xg_batch_view &v, size_t epoch) {
+  const uint32_t V = (uint32_t)e.ds.num_node;
+  if (!e.d_sanity) {
+    SAM_CUDA(cudaMalloc(&e.d_sanity, sizeof(uint64_t)));
+    SAM_CUDA(cudaMalloc(&e.d_epoch_map, (size_t)V * sizeof(uint32_t)));
+    e.sanity_epoch = (size_t)-1;
+  }
+  if (e.sanity_epoch != epoch) {
+    SAM_CUDA(cudaMemsetAsync(e.d_epoch_map, 0, (size_t)V * sizeof(uint32_t), e.stream));
+    e.sanity_epoch = epoch;
+  }
+  SAM_CUDA(cudaMemsetAsync(e.d_sanity, 0, sizeof(uint64_t), e.stream));
+  // duplicates are legal only as the shuffler's padding (<= num_worker - 1 per epoch, dist_shuffler_aligned.cc:53-55),
+  // so the epoch map is only armed when nothing was padded
+  const bool padded = (e.ds.num_train % g_cfg.num_worker) != 0;
+  SAM_XG(xg_sanity_check_ids(v.output_nodes, v.num_output, V, padded ? nullptr : e.d_epoch_map, e.d_sanity, e.stream));
+  SAM_XG(xg_sanity_check_ids(v.input_nodes, v.num_input, V, nullptr, e.d_sanity, e.stream));
+  for (uint32_t l = 0; l < v.num_layer; ++l)
+    SAM_XG(xg_sanity_check_edges(v.row[l], v.col[l], v.num_edge[l], (uint32_t)v.num_src[l], (uint32_t)v.num_dst[l], e.d_sanity,
+                                 e.stream));
+  uint64_t bad = 0;
+  SAM_CUDA(cudaMemcpyAsync(&bad, e.d_sanity, sizeof(bad), cudaMemcpyDeviceToHost, e.stream));
+  SAM_CUDA(cudaStreamSynchronize(e.stream));
+  SAM_CHECK_MSG(bad == 0, "SAMGRAPH_SANITY_CHECK: " + std::to_string(bad) + " violation(s) in batch " + std::to_string(v.key));
+}
+
 bool produce_one(Engine &e) {
   SAM_CHECK_MSG(e.sampler_ready, "sample_init / init has not run");
   create_sampler(e);
@@ -688,6 +723,7 @@ bool produce_one(Engine &e) {
   }
   SAM_XG(xg_batch_wait(holder->batch, &holder->view));
   const double t_total = now_s() - t0;
+  if (e.sanity_check) sanity_check_batch(e, holder->view, epoch);
   double edges = 0;
   for (uint32_t l = 0; l < holder->view.num_layer; ++l) edges += (double)holder->view.num_edge[l];
   const double feat_bytes = (double)holder->view.num_input * e.ds.feat_row_bytes();

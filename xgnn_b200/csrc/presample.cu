@@ -93,3 +93,66 @@ int xg_presample_rank(const uint32_t *d_freq, uint32_t num_node, uint32_t *d_ran
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// SAMGRAPH_SANITY_CHECK (reference: GPUBatchSanityCheck / GPUSanityCheckList, cuda/cuda_sanity_check.cu:28-88,
+// called from GPUShuffler::GetBatch, cuda/cuda_shuffler.cc:145-152; CPUSanityCheckNoDuplicate,
+// cpu/cpu_sanity_check.cc:29-45).  The reference asserts inside the kernel; here violations are COUNTED
+// (one launch per list, no printf from the device) and the caller decides what to do with the count.
+//   seeds:  no kEmptyKey, every id < num_node, and - with an epoch map - not seen before in this epoch
+//   edges:  row[e] < num_src, col[e] < num_dst
+namespace xg {
+namespace {
+
+__global__ void __launch_bounds__(256)
+sanity_ids_kernel(const uint32_t *__restrict__ ids, size_t n, uint32_t num_node, uint32_t *epoch_map,
+                  unsigned long long *violations) {
+  unsigned long long bad = 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const uint32_t v = ids[i];
+    if (v == kEmpty || v >= num_node) {
+      ++bad;
+    } else if (epoch_map != nullptr && atomicExch(epoch_map + v, 1u) != 0u) {
+      ++bad;  // "duplicate batch input", cuda_sanity_check.cu:37-41
+    }
+  }
+  if (bad) atomicAdd(violations, bad);
+}
+
+__global__ void __launch_bounds__(256)
+sanity_edges_kernel(const uint32_t *__restrict__ row, const uint32_t *__restrict__ col, size_t n, uint32_t num_src,
+                    uint32_t num_dst, unsigned long long *violations) {
+  unsigned long long bad = 0;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    if (row[i] >= num_src || col[i] >= num_dst) ++bad;
+  if (bad) atomicAdd(violations, bad);
+}
+
+}  // namespace
+}  // namespace xg
+
+extern "C" {
+
+int xg_sanity_check_ids(const uint32_t *d_ids, size_t n, uint32_t num_node, uint32_t *d_epoch_map,
+                        uint64_t *d_violations, void *stream) {
+  XG_REQUIRE(d_violations != nullptr, "d_violations is NULL");
+  if (n == 0) return XG_OK;
+  XG_REQUIRE(d_ids != nullptr, "d_ids is NULL");
+  sanity_ids_kernel<<<grid_for((n + 255) / 256, 8), 256, 0, as_stream(stream)>>>(
+      d_ids, n, num_node, d_epoch_map, reinterpret_cast<unsigned long long *>(d_violations));
+  XG_LAUNCHED();
+  return XG_OK;
+}
+
+int xg_sanity_check_edges(const uint32_t *d_row, const uint32_t *d_col, size_t n, uint32_t num_src, uint32_t num_dst,
+                          uint64_t *d_violations, void *stream) {
+  XG_REQUIRE(d_violations != nullptr, "d_violations is NULL");
+  if (n == 0) return XG_OK;
+  XG_REQUIRE(d_row && d_col, "NULL edge list");
+  sanity_edges_kernel<<<grid_for((n + 255) / 256, 8), 256, 0, as_stream(stream)>>>(
+      d_row, d_col, n, num_src, num_dst, reinterpret_cast<unsigned long long *>(d_violations));
+  XG_LAUNCHED();
+  return XG_OK;
+}
+
+}  // extern "C"

@@ -451,6 +451,24 @@ def presample_rank(sampler: "MinibatchSampler", num_node: int, batches, key0: in
     return rank_nodes, rank_freq
 
 
+def sanity_check_ids(ids: torch.Tensor, num_node: int, epoch_map: torch.Tensor | None = None) -> int:
+    """GPUBatchSanityCheck / GPUSanityCheckList (cuda/cuda_sanity_check.cu:28-88) as a count instead of a device assert:
+    ids equal to kEmptyKey, ids >= num_node and - with an `epoch_map` (int32[num_node], zero at the start of an epoch,
+    updated in place) - ids already seen this epoch."""
+    bad = torch.zeros(1, dtype=torch.int64, device=ids.device)
+    check(lib.xg_sanity_check_ids(_ptr(ids), ids.numel(), num_node, _ptr(epoch_map) if epoch_map is not None else None,
+                                  _ptr(bad), _stream()))
+    return int(bad.item())
+
+
+def sanity_check_edges(row: torch.Tensor, col: torch.Tensor, num_src: int, num_dst: int) -> int:
+    """number of edges whose local endpoints fall outside their block (row >= num_src or col >= num_dst)"""
+    assert row.numel() == col.numel()
+    bad = torch.zeros(1, dtype=torch.int64, device=row.device)
+    check(lib.xg_sanity_check_edges(_ptr(row), _ptr(col), row.numel(), num_src, num_dst, _ptr(bad), _stream()))
+    return int(bad.item())
+
+
 def predict_num_nodes(batch_size: int, fanout) -> int:
     arr = (c_uint32 * len(fanout))(*[int(f) for f in fanout])
     return int(lib.xg_predict_num_nodes(batch_size, arr, len(fanout)))
