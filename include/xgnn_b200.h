@@ -93,7 +93,9 @@ typedef struct xg_feature_store {
   uint64_t row_bytes;       /* dim * sizeof(dtype) */
   const void *replica;      /* rows of cache ranks [0, num_replicated) in THIS GPU's HBM, or NULL */
   uint32_t num_replicated;
-  uint32_t reserved;
+  uint32_t compact_bitwidth; /* 0: rank routing above.  b > 0 (needs num_replicated == 0): a cache_table value is
+                              * (part << (32 - b)) | row, the ICS'22 clique placement's compact map
+                              * (cuda/ics22_song_dist_feature.h:38-47, cuda_cache_manager_host.cc:203-222) */
 } xg_feature_store;
 
 /* ------------------------------------------------------------------------------------------------
@@ -316,6 +318,20 @@ size_t xg_predict_num_nodes(size_t batch_size, const uint32_t *fanout, size_t nu
 /* std::shuffle(nodes, nodes + n, std::mt19937(n)): the cache-rank order of GPUCacheManager,
  * cuda/cuda_cache_manager_host.cc:162-171 (same libstdc++ algorithm, hence the same order). */
 int xg_shuffle_cache_ranks(uint32_t *h_nodes, size_t num_cached);
+/* ICS'22 clique feature placement (comparison baseline): ICS22SongPlacementSolver, cuda/ics22_song_dist_feature.cc:22-167,
+ * seen from ONE worker.  h_rank_nodes / h_rank_weight: all nodes by weight descending (ties: node id descending) and
+ * their weights - the reference uses the in-degree (ics22_song_dist_feature.cc:196-213); xg_presample_accumulate over
+ * `indices` + xg_presample_rank produce exactly this pair.  Every GPU owns num_cached row slots; clique_size GPUs
+ * (worker / clique_size is the clique) split the coldest slots among themselves while
+ * weight(candidate) >= alpha * weight(slot's node).  Outputs, host memory:
+ *   h_cache_table u32[num_node]  (owner GPU << (32 - compact_bitwidth)) | row, XG_EMPTY_KEY = not cached
+ *                                (the compact map of cuda_cache_manager_host.cc:203-222; xg_feature_store.compact_bitwidth)
+ *   h_slot_nodes  u32[num_cached] node whose row sits in slot i of THIS worker's cache
+ *   h_total_cached               distinct nodes cached by the clique (GetRealCachedNodeNum) */
+int xg_ics22_placement(const uint32_t *h_rank_nodes, const uint32_t *h_rank_weight, uint32_t num_node,
+                       uint32_t num_cached, uint32_t num_dev, uint32_t clique_size, double alpha, uint32_t worker,
+                       uint32_t compact_bitwidth, uint32_t *h_cache_table, uint32_t *h_slot_nodes,
+                       uint32_t *h_total_cached);
 /* smallest n with indptr[n] >= floor(E * ratio): DistEngine::SampleDataCopy, dist/dist_engine.cc:223-232 */
 uint32_t xg_num_cache_node(const uint32_t *h_indptr, uint32_t num_node, double ratio);
 /* DistGraph::_DatasetPartition, cuda/dist_graph.cu:228-272, as two device passes around the caller's

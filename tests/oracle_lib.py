@@ -396,3 +396,83 @@ def minibatch_ext(g, seeds, fan, sample_type, seed, batch_key, rw=None):
         cur = table.unique()
     out["input_nodes"] = cur
     return out
+
+
+def ics22_in_degree_rank(indices, num_node):
+    """ICS22SongDistGraph ctor (cuda/ics22_song_dist_feature.cc:196-213) + the sort at :48-56: weight[v] = number of
+    times v occurs in `indices`, all nodes sorted by (weight, id) with std::greater (both descending)."""
+    w = np.bincount(u32(indices), minlength=num_node).astype(np.uint64)
+    words = np.sort((w << np.uint64(32)) | np.arange(num_node, dtype=np.uint64))[::-1]
+    return (words & np.uint64(0xFFFFFFFF)).astype(np.uint32), (words >> np.uint64(32)).astype(np.uint32)
+
+
+def ics22_placement(weight, num_cached, num_dev, clique_size, alpha):
+    """ICS22SongPlacementSolver (cuda/ics22_song_dist_feature.cc:22-167) restated for ALL devices at once, as the
+    reference runs it: returns (ranking u32[V], device_map[num_dev][V], new_idx_map[num_dev][V],
+    cached_nodes[num_dev][num_cached], total_cached).  Pure-Python loop: small cases only.
+    Parity unpinned by the reference's own tests (it has none for this solver); this follows the source line by line
+    in meaning: the per-device maps, the group-of-(c-1) device order refresh, the unsigned underflow stop."""
+    weight = np.asarray(weight, dtype=np.float64)
+    V = len(weight)
+    EMPTY = 0xFFFFFFFF
+    ranked = sorted(range(V), key=lambda v: (weight[v], v), reverse=True)  # std::greater<pair<double, IdType>>
+    dev_map = np.full((num_dev, V), EMPTY, np.uint32)
+    idx_map = np.full((num_dev, V), EMPTY, np.uint32)
+    cached = np.zeros((num_dev, num_cached), np.uint32)
+    for d in range(num_dev):
+        for i in range(num_cached):
+            idx_map[d, ranked[i]] = i
+            cached[d, i] = ranked[i]
+            dev_map[d, ranked[i]] = d
+    total = num_cached
+    if clique_size == 1:
+        return np.array(ranked, np.uint32), dev_map, idx_map, cached, total
+    p_accum = [0.0] * clique_size
+
+    def device_order():
+        return [d for _, d in sorted((p_accum[d], d) for d in range(clique_size))]
+
+    order = device_order()
+    num_cliques = num_dev // clique_size
+    i = 0
+    while i < V - num_cached:
+        if i % (clique_size - 1) == 0:
+            order = device_order()
+        cand = ranked[num_cached + i]
+        slot = num_cached - 1 - i // (clique_size - 1)
+        if slot < 0:  # IdType underflow -> ">= num_cached_node" -> break (:112-114)
+            break
+        victim = ranked[slot]
+        if not (weight[cand] >= alpha * weight[victim]):
+            break
+        cur = order[i % (clique_size - 1)]
+        p_accum[cur] += weight[cand]
+        for j in range(num_cliques):
+            for k in range(clique_size):
+                dev_map[j * clique_size + k, cand] = j * clique_size + cur
+                idx_map[j * clique_size + k, cand] = slot
+            dev_map[j * clique_size + cur, victim] = j * clique_size + order[-1]
+            cached[j * clique_size + cur, slot] = cand
+        i += 1
+    total = num_cached + i
+    return np.array(ranked, np.uint32), dev_map, idx_map, cached, total
+
+
+def ics22_compact_table(ranking, dev_map, idx_map, total_cached, device, bitwidth=3):
+    """GPUCacheManager's compact hashtable for one worker (cuda/cuda_cache_manager_host.cc:203-222):
+    table[node] = (device_map[node] << (32 - b)) | idx_map[node] for node in ranking[:total_cached]."""
+    shift = 32 - bitwidth
+    table = np.full(dev_map.shape[1], 0xFFFFFFFF, np.uint32)
+    nodes = u32(ranking[:total_cached])
+    table[nodes] = ((dev_map[device, nodes].astype(np.uint64) << np.uint64(shift)) | idx_map[device, nodes]).astype(np.uint32)
+    return table
+
+
+def extract_ics22(parts, table, host_feat, nodes, bitwidth=3):
+    """DeviceICS22SongDistFeature::Get (cuda/ics22_song_dist_feature.h:28-47) for cached nodes, host rows otherwise"""
+    shift = 32 - bitwidth
+    out = np.empty((len(nodes), host_feat.shape[1]), host_feat.dtype)
+    for i, v in enumerate(u32(nodes)):
+        t = int(table[v])
+        out[i] = host_feat[v] if t == 0xFFFFFFFF else parts[t >> shift][t & ((1 << shift) - 1)]
+    return out

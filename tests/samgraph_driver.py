@@ -150,6 +150,10 @@ def main():
     extra = {"num_worker": num_worker, "part_cache": "True", "gpu_extract": "True"}
     if uniform:
         extra["use_dist_graph"] = 0.7  # weighted tables need the flat CSR
+    if os.environ.get("XG_TEST_ICS22"):  # "clique_size,alpha": the ICS'22 clique placement instead of the GGMS partition cache
+        clique, alpha = os.environ["XG_TEST_ICS22"].split(",")
+        del extra["part_cache"]
+        extra.update(use_ics22_song_solver="True", clique_size=int(clique), ics22_song_alpha=float(alpha), use_dist_graph=0.7)
     fan = run_config(sam, d, sample_type, g, sam.kArch6, extra)
     sam.data_init()  # before fork, no CUDA in the parent (train_graphsage.py:386-402)
     pids = []

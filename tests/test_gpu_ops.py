@@ -355,3 +355,62 @@ def test_sanity_check_counts_violations():
     assert ops.sanity_check_edges(row, col, 50, 20) == 0
     want = int(((row >= 40) | (col >= 15)).sum())
     assert ops.sanity_check_edges(row, col, 40, 15) == want and want > 0
+
+
+@pytest.mark.parametrize("num_dev,clique,alpha,pct", [(4, 4, 0.0, 0.1), (4, 2, 0.5, 0.2), (8, 8, 0.2, 0.05), (2, 1, 0.0, 0.3)])
+def test_extract_through_ics22_compact_map(num_dev, clique, alpha, pct):
+    """ICS'22 clique placement end to end at the operator level: rank by in-degree on the GPU (xg_presample_accumulate
+    over `indices` + xg_presample_rank) == the oracle's ranking; every worker's xg_ics22_placement view; one gather launch
+    through the compact (owner << 29 | row) map == DeviceICS22SongDistFeature::Get for cached nodes and host rows for the
+    rest (cuda/ics22_song_dist_feature.h:28-47), bit for bit.  All `GPUs` are buffers of this one device."""
+    import ctypes
+    from xgnn_b200 import ops
+    from xgnn_b200._clib import check, lib
+    V, E, dim = 6000, 90000, 24
+    indptr, indices = synth.make_graph(V, E, seed=11, max_deg=400)
+    feat = synth.make_features(V, dim)
+    want_nodes, want_w = O.ics22_in_degree_rank(indices, V)
+    d_idx = torch.from_numpy(indices.view(np.int32)).cuda()
+    freq = torch.zeros(V, dtype=torch.int32, device="cuda")
+    check(lib.xg_presample_accumulate(freq.data_ptr(), V, d_idx.data_ptr(), d_idx.numel(), None, None))
+    rank_nodes = torch.empty(V, dtype=torch.int32, device="cuda")
+    rank_w = torch.empty(V, dtype=torch.int32, device="cuda")
+    check(lib.xg_presample_rank(freq.data_ptr(), V, rank_nodes.data_ptr(), rank_w.data_ptr(), None))
+    h_nodes, h_w = rank_nodes.cpu().numpy().view(np.uint32), rank_w.cpu().numpy().view(np.uint32)
+    assert np.array_equal(h_nodes, want_nodes) and np.array_equal(h_w, want_w)
+    n_cached = int(V * pct)
+    weight = np.bincount(indices, minlength=V).astype(np.float64)
+    ranking, dev_map, idx_map, cached, total = O.ics22_placement(weight, n_cached, num_dev, clique, alpha)
+    parts_np = [feat[cached[d]] for d in range(num_dev)]  # FeatureLoad: CPUExtract of the device's slot list
+    d_parts = []
+    for w in range(num_dev):
+        table, slots, tot = np.empty(V, np.uint32), np.empty(n_cached, np.uint32), ctypes.c_uint32(0)
+        check(lib.xg_ics22_placement(h_nodes.ctypes.data, h_w.ctypes.data, V, n_cached, num_dev, clique, alpha, w, 3,
+                                     table.ctypes.data, slots.ctypes.data, ctypes.addressof(tot)))
+        assert tot.value == total and np.array_equal(slots, cached[w])
+        d_parts.append((torch.from_numpy(feat[slots]).cuda(), torch.from_numpy(table.view(np.int32)).cuda(), table))
+    host = torch.from_numpy(feat).cuda()  # the "host" slot of the handle (device memory stands in for pinned host rows)
+    rng = np.random.default_rng(1)
+    nodes = rng.integers(0, V, 5000).astype(np.uint32)
+    nodes[:50] = ranking[:50]  # the hottest nodes are in every batch
+    d_nodes = torch.from_numpy(nodes.view(np.int32)).cuda()
+    for w in range(num_dev):
+        st = ops.make_feature_store(dim * 4, host, d_parts[w][1], parts=[p[0] for p in d_parts], local_parts=(w,),
+                                    compact_bitwidth=3)
+        got = ops.ExtractGGMS(st, d_nodes, dim, torch.float32).cpu().numpy()
+        want = O.extract_ics22(parts_np, d_parts[w][2], feat, nodes)
+        assert np.array_equal(got.view(np.uint32), want.view(np.uint32))
+        assert np.array_equal(got.view(np.uint32), feat[nodes].view(np.uint32))  # placement never changes WHAT is read
+        stats = torch.zeros(4, dtype=torch.int64, device="cuda")
+        ops.ExtractGGMS(st, d_nodes, dim, torch.float32, stats=stats)
+        t = d_parts[w][2][nodes]
+        n_host = int((t == 0xFFFFFFFF).sum())
+        n_local = int(((t != 0xFFFFFFFF) & ((t >> 29) == w)).sum())
+        assert stats.cpu().tolist()[:3] == [n_local, len(nodes) - n_host - n_local, n_host]
+        # the reference's three-step form (GetMissCacheIndex -> GPUExtractMissData -> CombineCacheData with the compact
+        # values as cache src, cuda_cache_manager_device.cu:355-441,573-731) gives the same rows
+        gms, gmd, gcs, gcd = ops.GetMissCacheIndex(d_parts[w][1], d_nodes)
+        out2 = torch.empty((len(nodes), dim), dtype=torch.float32, device="cuda")
+        ops.GPUExtractMissData(out2, host, gms, gmd, dim * 4)
+        ops.CombineCacheData(out2, st, gcs, gcd)
+        assert np.array_equal(out2.cpu().numpy().view(np.uint32), want.view(np.uint32))

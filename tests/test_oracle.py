@@ -206,3 +206,57 @@ def test_presample_rank_oracle_order():
     """freq descending, ties by node id descending (std::greater on {low: id, high: freq}, pre_sampler.cc:113-119)"""
     nodes, freq = O.presample_rank(6, [np.array([1, 3], np.uint32), np.array([3, 4], np.uint32), np.array([3, 1], np.uint32)])
     assert nodes.tolist() == [3, 1, 4, 5, 2, 0] and freq.tolist() == [3, 2, 1, 0, 0, 0]
+
+
+@pytest.mark.parametrize("V,n_cached,num_dev,clique,alpha", [
+    (200, 40, 4, 4, 0.0), (200, 40, 4, 2, 0.5), (300, 25, 8, 4, 0.9), (120, 30, 2, 2, 0.3), (64, 64, 4, 4, 0.0),
+    (150, 10, 6, 3, 0.0), (100, 20, 3, 1, 0.5), (90, 0, 2, 2, 0.0), (97, 5, 8, 8, 0.05)])
+def test_ics22_placement_matches_the_all_device_restatement(V, n_cached, num_dev, clique, alpha):
+    """xg_ics22_placement (one worker's view, single pass) against the oracle that keeps the reference's per-device
+    maps (cuda/ics22_song_dist_feature.cc:22-167): same compact table, same slot contents, same total; and the
+    layout is consistent - whatever GPU/row a worker's table names holds that node."""
+    import ctypes
+    from xgnn_b200._clib import check, lib
+    rng = np.random.default_rng(V * 31 + num_dev)
+    E = V * 12
+    indices = np.minimum((rng.pareto(1.2, E) * 3).astype(np.int64), V - 1).astype(np.uint32)  # skewed, many ties
+    rank_nodes, rank_w = O.ics22_in_degree_rank(indices, V)
+    weight = np.bincount(indices, minlength=V).astype(np.float64)
+    ranking, dev_map, idx_map, cached, total = O.ics22_placement(weight, n_cached, num_dev, clique, alpha)
+    assert np.array_equal(ranking, rank_nodes)
+    tables, slots = [], []
+    for w in range(num_dev):
+        table = np.empty(V, np.uint32)
+        slot_nodes = np.empty(max(n_cached, 1), np.uint32)
+        tot = ctypes.c_uint32(0)
+        check(lib.xg_ics22_placement(rank_nodes.ctypes.data, rank_w.ctypes.data, V, n_cached, num_dev, clique, alpha, w, 3,
+                                     table.ctypes.data, slot_nodes.ctypes.data, ctypes.addressof(tot)))
+        assert tot.value == total
+        assert np.array_equal(table, O.ics22_compact_table(ranking, dev_map, idx_map, total, w))
+        assert np.array_equal(slot_nodes[:n_cached], cached[w])
+        tables.append(table)
+        slots.append(slot_nodes[:n_cached])
+    assert int((tables[0] != 0xFFFFFFFF).sum()) == total
+    if clique > 1 and alpha == 0.0 and 0 < n_cached and n_cached * clique <= V:
+        assert total == n_cached * clique  # every slot split: the clique caches c x as many distinct nodes
+    for w in range(num_dev):
+        cached_nodes = np.nonzero(tables[w] != 0xFFFFFFFF)[0]
+        owner, row = tables[w][cached_nodes] >> 29, tables[w][cached_nodes] & ((1 << 29) - 1)
+        assert np.all(owner // clique == w // clique), "a worker only reads inside its clique"
+        for v, o, r in zip(cached_nodes, owner, row):
+            assert slots[o][r] == v
+
+
+def test_ics22_placement_rejects_bad_arguments():
+    import ctypes
+    from xgnn_b200._clib import lib
+    nodes, w = np.arange(8, dtype=np.uint32)[::-1].copy(), np.arange(8, dtype=np.uint32)[::-1].copy()
+    table, slots = np.zeros(8, np.uint32), np.zeros(8, np.uint32)
+    tot = ctypes.c_uint32(0)
+    args = lambda **k: (nodes.ctypes.data, w.ctypes.data, 8, k.get("n", 4), k.get("dev", 4), k.get("c", 2), 0.0,
+                        k.get("w", 0), k.get("b", 3), table.ctypes.data, slots.ctypes.data, ctypes.addressof(tot))
+    assert lib.xg_ics22_placement(*args()) == 0
+    assert lib.xg_ics22_placement(*args(c=3)) != 0   # 4 GPUs are not a multiple of 3
+    assert lib.xg_ics22_placement(*args(w=4)) != 0   # worker out of range
+    assert lib.xg_ics22_placement(*args(b=1)) != 0   # 1 bit cannot name 4 GPUs
+    assert lib.xg_ics22_placement(*args(n=9)) != 0   # more slots than nodes

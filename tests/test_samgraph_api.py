@@ -135,3 +135,14 @@ def test_sanity_check_env_flows(dataset, mode, args):
     kEmptyKey, out-of-range ids / edge endpoints and seeds repeated inside an epoch; a clean run must pass untouched."""
     import torch
     _drive(mode, dataset, *args, env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "SAMGRAPH_SANITY_CHECK": "1"})
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("workers,clique,alpha", [(2, 2, 0.0), (4, 2, 0.6), (3, 3, 0.3)])
+def test_arch6_ics22_clique_placement(dataset, workers, clique, alpha):
+    """`use_ics22_song_solver` (operation.cc:213-230): every worker ranks by in-degree on its GPU, solves its own view of
+    the ICS'22 clique placement, shares its cache over IPC inside the clique and gathers through the compact
+    (owner, row) map; every batch's features must still be CPUExtract's rows bit for bit."""
+    import torch
+    _drive("arch6", dataset, 0, workers,
+           env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "XG_TEST_ICS22": f"{clique},{alpha}"})

@@ -118,6 +118,10 @@ struct RunConfig {
   int sampler_device = 0, trainer_device = 0;
   size_t num_worker = 1;
   bool use_dist_graph = false, part_cache = false, gpu_extract = false;
+  bool use_ics22_song_solver = false;  // operation.cc:213-230
+  int clique_size = 0;
+  double ics22_song_alpha = 0.0;
+  int ics22_compact_bitwidth = 3;      // run_config.cc:99-100 (compact mode is the reference default)
   double dist_graph_percentage = 0.0;
   int omp_thread_num = 1;
 };
@@ -567,7 +571,8 @@ void build_feature_store(Engine &e) {
   if (n_cached > V) n_cached = V;
   if (n_cached < V) e.store.host = pin_host(ds.feat, V * row_bytes);  // misses: zero-copy UVA loads
   if (n_cached == 0) return;                                          // cache_table == NULL: every row from `host`
-  const bool parted = cfg.run_arch == kArch6 && cfg.part_cache && e.shared != nullptr;
+  const bool ics22 = cfg.run_arch == kArch6 && cfg.use_ics22_song_solver && e.shared != nullptr;
+  const bool parted = (cfg.run_arch == kArch6 && cfg.part_cache && e.shared != nullptr) || ics22;
   const uint32_t P = parted ? (uint32_t)e.shared->num_worker : 1u;
   if (!parted && n_cached == V) {
     // every row cached in one part: lay the part out by node id (where a cached row sits is ours to choose) and
@@ -586,7 +591,7 @@ void build_feature_store(Engine &e) {
   if (n_rep > n_cached) n_rep = n_cached;
   if (parted && n_cached > n_rep)
     SAM_XG(xg_shuffle_cache_ranks(ranks.data() + n_rep, n_cached - n_rep));  // cuda_cache_manager_host.cc:162-171
-  {
+  if (!ics22) {
     std::vector<uint32_t> table(V, XG_EMPTY_KEY);
     for (size_t r = 0; r < n_cached; ++r) table[ranks[r]] = (uint32_t)r;
     e.store.cache_table = to_device(e, table.data(), V);
@@ -606,6 +611,62 @@ void build_feature_store(Engine &e) {
     }
     return d_rows;
   };
+  if (ics22) {
+    // ICS'22 clique placement (comparison baseline; ICS22SongDistGraph ctor + FeatureLoad, cuda/ics22_song_dist_feature.cc:
+    // 169-305, and the compact map of cuda_cache_manager_host.cc:172-222).  The reference solves for every GPU in the
+    // parent before the fork; here each worker ranks the nodes by in-degree on its own GPU (same counts -> same order in
+    // every worker) and derives only its own view of the placement.
+    const uint32_t c = (uint32_t)cfg.clique_size, bw = (uint32_t)cfg.ics22_compact_bitwidth;
+    SAM_CHECK_MSG(P % c == 0, "num_worker must be a multiple of clique_size");
+    SAM_CHECK_MSG(P <= (1u << bw), "ics22 compact map: too many workers for ics22_compact_bitwidth");
+    std::vector<uint32_t> rank_nodes(V), rank_weight(V);
+    {
+      uint32_t *d_freq = nullptr, *d_rank = nullptr, *d_rfreq = nullptr, *d_chunk = nullptr;
+      const size_t chunk = std::min<size_t>(std::max<size_t>(ds.num_edge, 1), (size_t)64 << 20);
+      SAM_CUDA(cudaMalloc(&d_freq, V * sizeof(uint32_t)));
+      SAM_CUDA(cudaMalloc(&d_rank, V * sizeof(uint32_t)));
+      SAM_CUDA(cudaMalloc(&d_rfreq, V * sizeof(uint32_t)));
+      SAM_CUDA(cudaMalloc(&d_chunk, chunk * sizeof(uint32_t)));
+      SAM_CUDA(cudaMemsetAsync(d_freq, 0, V * sizeof(uint32_t), e.stream));
+      for (size_t off = 0; off < ds.num_edge; off += chunk) {  // weight = in-degree (:196-213)
+        const size_t n = std::min(chunk, ds.num_edge - off);
+        SAM_CUDA(cudaMemcpyAsync(d_chunk, ds.indices + off, n * sizeof(uint32_t), cudaMemcpyHostToDevice, e.stream));
+        SAM_XG(xg_presample_accumulate(d_freq, (uint32_t)V, d_chunk, n, nullptr, e.stream));
+        SAM_CUDA(cudaStreamSynchronize(e.stream));
+      }
+      SAM_XG(xg_presample_rank(d_freq, (uint32_t)V, d_rank, d_rfreq, e.stream));  // (weight, id) descending, as :48-56
+      SAM_CUDA(cudaMemcpy(rank_nodes.data(), d_rank, V * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+      SAM_CUDA(cudaMemcpy(rank_weight.data(), d_rfreq, V * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+      cudaFree(d_chunk); cudaFree(d_rfreq); cudaFree(d_rank); cudaFree(d_freq);
+    }
+    const int w = e.worker_id;
+    std::vector<uint32_t> table(V), slots(std::max<size_t>(n_cached, 1));
+    uint32_t total = 0;
+    SAM_XG(xg_ics22_placement(rank_nodes.data(), rank_weight.data(), (uint32_t)V, (uint32_t)n_cached, P, c,
+                              cfg.ics22_song_alpha, (uint32_t)w, bw, table.data(), slots.data(), &total));
+    e.store.cache_table = to_device(e, table.data(), V);
+    e.store.compact_bitwidth = bw;
+    e.store.num_part = P;
+    e.store.local_part_mask = 1u << w;
+    void *d_mine = gather_rows_to_device(slots.data(), n_cached);
+    SAM_XG(xg_ipc_export(d_mine, e.shared->feat[w][w]));
+    barrier(e);
+    const uint32_t first = (uint32_t)w / c * c;
+    for (uint32_t g = first; g < first + c; ++g) {  // only the clique's caches are ever named by the map (:258-274)
+      if ((int)g == w) {
+        e.store.part[g] = d_mine;
+      } else {
+        void *a = nullptr;
+        SAM_XG(xg_ipc_import(e.shared->feat[g][g], &a));
+        e.store.part[g] = a;
+      }
+    }
+    barrier(e);
+    if (w == 0)
+      std::fprintf(stderr, "[samgraph] ics22 clique placement: %zu rows per GPU, %u distinct nodes per clique of %u (alpha %.3f)\n",
+                   n_cached, total, c, cfg.ics22_song_alpha);
+    return;
+  }
   if (n_rep) {
     e.store.replica = gather_rows_to_device(ranks.data(), n_rep);
     e.store.num_replicated = (uint32_t)n_rep;
@@ -923,8 +984,16 @@ void samgraph_config(const char **keys, const char **vals, const size_t n) {
     SAM_CHECK_MSG(c.run_arch == kArch6, "partition cache can only be used in arch6");  // operation.cc:205-211
     c.part_cache = true;
   }
-  if (m.count("use_ics22_song_solver") && m["use_ics22_song_solver"] == "True")
-    fatal(__FILE__, __LINE__, "the ICS'22 clique placement is a comparison baseline: out of scope");
+  if (m.count("clique_size")) c.clique_size = std::stoi(m["clique_size"]);              // operation.cc:213-216
+  if (m.count("ics22_song_alpha")) c.ics22_song_alpha = std::stod(m["ics22_song_alpha"]);  // :217-220
+  if (m.count("use_ics22_song_solver") && m["use_ics22_song_solver"] == "True") {       // :221-230
+    SAM_CHECK_MSG(c.use_dist_graph, "use ics22_song_solver need to open dist_graph");
+    SAM_CHECK_MSG(!c.part_cache, "use ics22_song_solver need to close part cache");
+    SAM_CHECK_MSG(c.clique_size > 0, "use ics22_song_solver need to set clique size");
+    SAM_CHECK_MSG(c.run_arch == kArch6, "ics22_song_solver can only be used in arch6");
+    SAM_CHECK_MSG(c.cache_policy == kCacheByDegree, "ics22_song_solver only support degree at present platform");  // cuda_cache_manager_host.cc:173-174
+    c.use_ics22_song_solver = true;
+  }
   c.gpu_extract = m.count("gpu_extract") && m["gpu_extract"] == "True";
   if (m.count("unified_memory") && m["unified_memory"] == "True")
     fatal(__FILE__, __LINE__, "unified-memory sampling (arch9 / UM) is out of scope");

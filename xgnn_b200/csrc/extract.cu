@@ -66,6 +66,20 @@ template <> __device__ __forceinline__ void st_stream<int4>(int4 *p, const int4 
                "r"(v.z), "r"(v.w) : "memory");
 }
 
+// cache-table value -> (part, row).  Default: DeviceDistFeature::Get (cuda/dist_graph.h:203-207), part r % P, row r / P.
+// compact_bitwidth != 0: DeviceICS22SongDistFeature::_GetRealPartId (cuda/ics22_song_dist_feature.h:38-47), the value
+// carries the owning GPU in its top bits and the row in the rest.
+__device__ __forceinline__ void split_rank(const xg_feature_store &st, uint32_t rank, uint32_t *part, uint32_t *row) {
+  if (st.compact_bitwidth) {
+    const uint32_t shift = 32u - st.compact_bitwidth;
+    *part = rank >> shift;
+    *row = rank & ((1u << shift) - 1u);
+  } else {
+    *part = rank % st.num_part;
+    *row = rank / st.num_part;
+  }
+}
+
 __device__ __forceinline__ const char *route_row(const xg_feature_store &st, int mode, uint32_t idx,
                                                  int *klass) {
   uint32_t rank = kEmpty;
@@ -80,9 +94,10 @@ __device__ __forceinline__ const char *route_row(const xg_feature_store &st, int
     return static_cast<const char *>(st.replica) + (size_t)rank * st.row_bytes;
   }
   rank -= st.num_replicated;
-  const uint32_t part = rank % st.num_part;
+  uint32_t part, row;
+  split_rank(st, rank, &part, &row);
   *klass = ((st.local_part_mask >> part) & 1u) ? 0 : 1;
-  return static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
+  return static_cast<const char *>(st.part[part]) + (size_t)row * st.row_bytes;
 }
 
 // One warp owns 32 consecutive rows at a time (a "group"); nothing in the kernel crosses a warp, so
@@ -148,9 +163,10 @@ gather_rows_kernel(const xg_feature_store st, int mode, const uint32_t *__restri
         sp = static_cast<const char *>(st.replica) + (size_t)rank * st.row_bytes;
       } else {
         rank -= st.num_replicated;
-        const uint32_t part = rank % st.num_part;
+        uint32_t part, row;
+        split_rank(st, rank, &part, &row);
         klass = ((st.local_part_mask >> part) & 1u) ? 0 : 1;
-        sp = static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
+        sp = static_cast<const char *>(st.part[part]) + (size_t)row * st.row_bytes;
       }
       const size_t drow = dst_idx ? (size_t)dst_idx[row0 + lane] : row0 + lane;
       dp = out + drow * st.row_bytes;
@@ -251,8 +267,9 @@ gather_rows_ring_kernel(const xg_feature_store st, int mode, const uint32_t *__r
     if (rank == kEmpty) return static_cast<const char *>(st.host) + (size_t)idx * st.row_bytes;
     if (rank < st.num_replicated) return static_cast<const char *>(st.replica) + (size_t)rank * st.row_bytes;
     rank -= st.num_replicated;
-    const uint32_t part = rank % st.num_part;
-    return static_cast<const char *>(st.part[part]) + (size_t)(rank / st.num_part) * st.row_bytes;
+    uint32_t part, row;
+    split_rank(st, rank, &part, &row);
+    return static_cast<const char *>(st.part[part]) + (size_t)row * st.row_bytes;
   };
   auto dst_of = [&](uint32_t g, uint32_t rows) -> char * {
     if (lane >= rows) return nullptr;

@@ -208,7 +208,8 @@ def GPUExtract(src: torch.Tensor | int, index: torch.Tensor, dim: int | None = N
 
 
 def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_table: torch.Tensor | None = None,
-                       parts=None, local_parts=(), replica=None, num_replicated: int = 0) -> XgFeatureStore:
+                       parts=None, local_parts=(), replica=None, num_replicated: int = 0,
+                       compact_bitwidth: int = 0) -> XgFeatureStore:
     """DeviceDistFeature + cache table + host table in one handle (cuda/dist_graph.h:182-213)."""
     st = XgFeatureStore()
 
@@ -229,6 +230,8 @@ def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_ta
     st.local_part_mask = mask
     st.replica = p(replica) if num_replicated else None
     st.num_replicated = num_replicated if replica is not None else 0
+    assert not (compact_bitwidth and st.num_replicated), "the compact (ICS'22) map has no replicated tier of its own"
+    st.compact_bitwidth = compact_bitwidth
     st._keep = [host, cache_table, parts, replica]  # raw pointers inside: keep the tensors alive
     return st
 
