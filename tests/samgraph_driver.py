@@ -130,6 +130,82 @@ def consume(sam, g, fan, sample_type, worker, num_worker, background):
     sam.shutdown()
 
 
+def run_arch5(sam, g, d, sample_type, num_sampler, num_trainer):
+    """arch5 (example/samgraph/multi_gpu/train_graphsage.py): S sampler processes and T trainer processes; a Task is
+    sampled in one process / GPU and its features are gathered in another.  Trainers take Tasks off one shared queue in
+    whatever order they arrive, so every batch is checked by its KEY: key -> (epoch, sampler, local step) -> the seeds
+    DistAlignedShuffler gives that sampler for that step."""
+    import torch
+    ngpu = int(os.environ.get("XG_TEST_NUM_GPU", "1"))
+    fan = run_config(sam, d, sample_type, g, sam.kArch5, {"num_sample_worker": num_sampler, "num_train_worker": num_trainer})
+    sam.data_init()
+    pids = []
+
+    def fork(fn):
+        pid = os.fork()
+        if pid == 0:
+            try:
+                fn()
+                os._exit(0)
+            except BaseException:  # noqa: BLE001
+                import traceback
+                traceback.print_exc()
+                os._exit(1)
+        pids.append(pid)
+
+    def sampler(w):
+        sam.sample_init(w, f"cuda:{w % ngpu}")
+        local = sam.num_local_step()
+        assert sam.steps_per_epoch() == local * num_sampler
+        for _ in range(EPOCHS * local):
+            sam.sample_once()
+        assert sam.get_log_epoch_value(0, sam.kLogEpochSampleTime) > 0
+        sam.shutdown()  # returns once every Task this sampler sent has been pulled
+
+    def trainer(t):
+        sam.train_init(t, f"cuda:{(num_sampler + t) % ngpu}")  # a different GPU than the samplers when the box has one
+        num_step, local = sam.steps_per_epoch(), sam.num_local_step()
+        total = EPOCHS * num_step
+        mine = total // num_trainer + (1 if t < total % num_trainer else 0)
+        expected = [expected_batches(g, w, num_sampler) for w in range(num_sampler)]
+        background = t % 2 == 1
+        if background:
+            sam.extract_start(mine)
+        seen, held = [], None
+        for _ in range(mine):
+            if not background:
+                sam.sample_once()
+            key = sam.get_next_batch()
+            ep, step = divmod(key, num_step)
+            w, st = divmod(step, local)
+            feat = check_batch(sam, g, key, expected[w][ep][st], fan, sample_type)
+            if held is None:
+                held, held_copy = feat, feat.clone()
+            assert sam.get_log_step_value_by_key(key, sam.kLogL1NumNode) == feat.shape[0]
+            seen.append(key)
+        assert len(set(seen)) == len(seen), "a Task was delivered twice"
+        assert torch.equal(held, held_copy), "a held batch tensor was overwritten"
+        with open(os.path.join(d, f"arch5_keys_{os.getppid()}_{t}.txt"), "w") as f:
+            f.write(" ".join(map(str, seen)))
+        sam.shutdown()
+
+    for w in range(num_sampler):
+        fork(lambda w=w: sampler(w))
+    for t in range(num_trainer):
+        fork(lambda t=t: trainer(t))
+    bad = sum(sam.wait_one_child() for _ in pids)
+    assert bad == 0, f"{bad} process(es) failed"
+    # every Task of every epoch reached exactly one trainer
+    keys = []
+    for t in range(num_trainer):
+        fn = os.path.join(d, f"arch5_keys_{os.getpid()}_{t}.txt")
+        keys += [int(x) for x in open(fn).read().split()]
+        os.remove(fn)
+    num_step = -(-(-(-len(g["train"]) // num_sampler)) // BATCH) * num_sampler
+    assert sorted(keys) == list(range(EPOCHS * num_step)), "Tasks lost or duplicated across trainers"
+    print("DRIVER OK")
+
+
 def main():
     mode, d, sample_type = sys.argv[1], sys.argv[2], int(sys.argv[3])
     import xgnn_b200.samgraph.torch as sam
@@ -142,6 +218,9 @@ def main():
         assert np.array_equal(sam.get_dataset_label().numpy(), g["label"])
         consume(sam, g, fan, sample_type, 0, 1, background)
         print("DRIVER OK")
+        return
+    if mode == "arch5":
+        run_arch5(sam, g, d, sample_type, int(sys.argv[4]), int(sys.argv[5]))
         return
     num_worker = int(sys.argv[4])
     import torch

@@ -59,8 +59,12 @@ def test_config_twice_and_out_of_scope_arch_abort(dataset):
             "'fanout': [3], 'num_fanout': 1, 'num_sample_worker': 1, 'num_train_worker': 1}\n" % dataset)
     r = _run_py(base % 3 + "sam.config(cfg)\nsam.config(cfg)")
     assert r.returncode != 0 and "is_configured" in r.stderr
-    r = _run_py(base % 5 + "sam.config(cfg)")
+    r = _run_py(base % 9 + "sam.config(cfg)")  # arch9 = unified-memory sampler
     assert r.returncode != 0 and "out of scope" in r.stderr
+    r = _run_py(base % 5 + "cfg['have_switcher'] = 1\nsam.config(cfg)")  # arch5 itself is built, its switcher is not
+    assert r.returncode != 0 and "out of scope" in r.stderr
+    r = _run_py(base % 5 + "sam.config(cfg)\nsam.data_init()\nprint(sam.steps_per_epoch(), sam.num_local_step())")
+    assert r.returncode == 0, r.stderr[-2000:]
     r = _run_py(base % 3 + "sam.config(cfg)\nprint('configured')")
     assert r.returncode == 0 and "configured" in r.stdout
 
@@ -146,3 +150,14 @@ def test_arch6_ics22_clique_placement(dataset, workers, clique, alpha):
     import torch
     _drive("arch6", dataset, 0, workers,
            env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "XG_TEST_ICS22": f"{clique},{alpha}"})
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sample_type,samplers,trainers", [(0, 1, 1), (0, 2, 2), (7, 2, 1), (3, 1, 2)])
+def test_arch5_decoupled_sampler_and_trainer_processes(dataset, sample_type, samplers, trainers):
+    """arch5: samplers and trainers are separate processes (separate GPUs when the box has them); a Task's
+    topology crosses as ONE peer copy out of the sampler's HBM, only a descriptor goes through host shared memory
+    (reference: D2H + 50 MB host ring + H2D, memory_queue.cc / task_queue.cc).  Every Task reaches exactly one trainer
+    and carries the oracle's blocks and CPUExtract's rows bit for bit."""
+    import torch
+    _drive("arch5", dataset, sample_type, samplers, trainers, env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count()))})

@@ -63,11 +63,20 @@ def main():
     ap.add_argument("--batch", type=int, default=8000)
     ap.add_argument("--dir", default="/dev/shm/xg_ds")
     ap.add_argument("--background", action="store_true", help="sam.start(): a producer thread samples ahead of the consumer")
+    ap.add_argument("--arch5", action="store_true", help="decoupled: sampler process(es) on the first GPUs, trainer process(es) on the next")
+    ap.add_argument("--samplers", type=int, default=1)
+    ap.add_argument("--trainers", type=int, default=1)
+    ap.add_argument("--dump-only", action="store_true")
     a = ap.parse_args()
+    if a.arch5:
+        return main_arch5(a)
     torch.cuda.set_device(0)
     t0 = time.perf_counter()
     V, E, T = dump_dataset(a.dir, a.shape, a.scale)
     t_dump = time.perf_counter() - t0
+    if a.dump_only:
+        print(json.dumps({"num_node": V, "num_edge": E, "train_set": T}))
+        return
 
     import xgnn_b200.samgraph.torch as sam
     fanout = [5, 10, 15]
@@ -107,6 +116,91 @@ def main():
                       "epochs": per_epoch, "dump_s": round(t_dump, 1), "init_s": round(t_init, 1),
                       "note": "one batch at a time (sample_once -> get_next_batch -> get_dgl_blocks): no look-ahead, "
                               "so the two phases of consecutive batches do not overlap as they do under bench.py"}))
+
+
+def main_arch5(a):
+    """S sampler processes (cuda:0..S-1) -> task queue -> T trainer processes (cuda:S..), as multi_gpu/train_graphsage.py
+    runs arch5; no model.  The parent must not touch CUDA before the fork, so the dataset is dumped by a child."""
+    import subprocess
+    r = subprocess.run([sys.executable, __file__, "--dump-only", "--shape", a.shape, "--scale", str(a.scale), "--dir", a.dir],
+                       capture_output=True, text=True, check=True)
+    meta = json.loads(r.stdout.strip().splitlines()[-1])
+    import xgnn_b200.samgraph.torch as sam
+    ngpu = int(os.environ.get("XG_NUM_GPU", "0")) or int(subprocess.run(
+        ["nvidia-smi", "-L"], capture_output=True, text=True).stdout.count("GPU "))
+    S, T = a.samplers, a.trainers
+    sam.config({"dataset_path": a.dir, "_arch": sam.kArch5, "_sample_type": sam.kKHop3, "batch_size": a.batch,
+                "num_epoch": a.epochs, "_cache_policy": sam.kCacheByDegree, "cache_percentage": 1.0,
+                "max_sampling_jobs": 10, "max_copying_jobs": 2, "omp_thread_num": 8, "num_layer": 3, "num_hidden": 256,
+                "lr": 0.003, "dropout": 0.5, "fanout": [5, 10, 15], "num_fanout": 3, "num_sample_worker": S,
+                "num_train_worker": T})
+    sam.data_init()
+    pids = []
+
+    def fork(fn):
+        pid = os.fork()
+        if pid == 0:
+            try:
+                fn()
+                os._exit(0)
+            except BaseException:  # noqa: BLE001
+                import traceback
+                traceback.print_exc()
+                os._exit(1)
+        pids.append(pid)
+
+    def sampler(w):
+        sam.sample_init(w, f"cuda:{w % ngpu}")
+        for _ in range(a.epochs * sam.num_local_step()):
+            sam.sample_once()
+        sam.shutdown()
+
+    def trainer(t):
+        dev = (S + t) % ngpu
+        sam.train_init(t, f"cuda:{dev}")
+        torch.cuda.set_device(dev)
+        steps = sam.steps_per_epoch()
+        total = a.epochs * steps
+        mine = total // T + (1 if t < total % T else 0)
+        warm = steps // T  # about one epoch of this trainer's share
+        sam.extract_start(mine)
+        edges = rows = nbytes = 0
+        recv = copy = 0.0
+        t0 = None
+        for i in range(mine):
+            if i == warm:
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+            key = sam.get_next_batch()
+            blocks, feat, label = sam.get_dgl_blocks(key, 3)
+            if i >= warm:
+                e = sum(sam.get_graph_num_edge(key, l) for l in range(3))
+                edges += e
+                rows += feat.shape[0]
+                nbytes += 4 * (feat.shape[0] + label.shape[0] + 2 * e + sum(b[3] + 1 for b in blocks))
+                recv += sam.get_log_step_value_by_key(key, sam.kLogL1RecvTime)
+                copy += sam.get_log_step_value_by_key(key, sam.kLogL1CopyTime)
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        n = mine - warm
+        with open(os.path.join(a.dir, f"arch5_{t}.json"), "w") as f:
+            json.dump({"trainer": t, "device": dev, "batches": n, "s": dt, "edges": edges, "rows": rows,
+                       "task_MB": nbytes / n / 1e6, "recv_ms": 1e3 * recv / n, "extract_ms": 1e3 * copy / n}, f)
+        sam.shutdown()
+
+    for w in range(S):
+        fork(lambda w=w: sampler(w))
+    for t in range(T):
+        fork(lambda t=t: trainer(t))
+    bad = sum(sam.wait_one_child() for _ in pids)
+    assert bad == 0
+    per = [json.load(open(os.path.join(a.dir, f"arch5_{t}.json"))) for t in range(T)]
+    print(json.dumps({"api": "samgraph.torch arch5 (decoupled sampler / trainer processes)", "shape": a.shape, "scale": a.scale,
+                      **meta, "samplers": S, "trainers": T, "gpus": ngpu, "batch": a.batch,
+                      "sampled_edges_per_s": sum(p["edges"] for p in per) / max(p["s"] for p in per),
+                      "trainers_detail": per,
+                      "note": "recv_ms = dequeue + ONE peer copy of the packed Task out of the sampler's HBM (incl. waiting "
+                              "for the sampler); extract_ms = feature + label gather on the trainer GPU"}))
 
 
 if __name__ == "__main__":

@@ -16,6 +16,7 @@
 // travel through one MAP_SHARED block created in data_init, guarded by a process-shared pthread barrier.
 #include <fcntl.h>
 #include <pthread.h>
+#include <semaphore.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
 #include <sys/wait.h>
@@ -29,6 +30,7 @@
 #include <cstring>
 #include <deque>
 #include <fstream>
+#include <functional>
 #include <iostream>
 #include <map>
 #include <memory>
@@ -118,6 +120,7 @@ struct RunConfig {
   int sampler_device = 0, trainer_device = 0;
   size_t num_worker = 1;
   bool use_dist_graph = false, part_cache = false, gpu_extract = false;
+  size_t num_train_worker = 0;         // arch5 (num_worker = num_sample_worker there)
   bool use_ics22_song_solver = false;  // operation.cc:213-230
   int clique_size = 0;
   double ics22_song_alpha = 0.0;
@@ -274,10 +277,11 @@ namespace sam {
 // ---------------------------------------------------------------------------------------------------
 // Profiler, reduced to what the Python side reads back (profiler.h:30-243; the enum numbering is ABI)
 constexpr int kNumLogInitItems = 32, kNumLogStepItems = 64, kNumLogEpochItems = 16;
-constexpr int kLogL1NumSample = 0, kLogL1NumNode = 1, kLogL1SampleTotalTime = 2, kLogL1SampleTime = 3, kLogL1CopyTime = 6,
+constexpr int kLogL1NumSample = 0, kLogL1NumNode = 1, kLogL1SampleTotalTime = 2, kLogL1SampleTime = 3, kLogL1SendTime = 4,
+              kLogL1RecvTime = 5, kLogL1CopyTime = 6,
               kLogL1FeatureBytes = 9, kLogL1LabelBytes = 10, kLogL1IdBytes = 11, kLogL1GraphBytes = 12,
               kLogL2ShuffleTime = 17, kLogL2CoreSampleTime = 20;
-constexpr int kLogEpochSampleTime = 0, kLogEpochSampleTotalTime = 3, kLogEpochCopyTime = 8, kLogEpochFeatureBytes = 12,
+constexpr int kLogEpochSampleTime = 0, kLogEpochSampleSendTime = 2, kLogEpochSampleTotalTime = 3, kLogEpochCopyTime = 8, kLogEpochFeatureBytes = 12,
               kLogEpochNumSample = 15;
 constexpr int kLogInitL1Common = 0, kLogInitL1Sampler = 1, kLogInitL1Trainer = 2, kLogInitL2LoadDataset = 6,
               kLogInitL2Presample = 8, kLogInitL2BuildCache = 10;
@@ -380,6 +384,34 @@ struct AlignedShuffler {
 // Cross-process state created by data_init before fork (DistGraph::Create, cuda/dist_graph.cu:566-631): the
 // placement, a process-shared barrier and the CUDA IPC handles of every shard.
 constexpr int kMaxWorker = XG_MAX_PARTS;
+// ---------------------------------------------------------------------------------------------------
+// arch5: samplers and trainers are different processes on different GPUs.  The reference moves every
+// Task through a host shared-memory ring: D2H of ids + per-layer row/col into a fixed 50 MB slot, memcpy, then H2D on
+// the trainer (MemoryQueue, memory_queue.h:65-130, memory_queue.cc:69-141; TransData/ToData/ParseData, task_queue.cc:
+// 66-330).  Here only a ~400-byte descriptor crosses host shared memory; the payload is packed once into a "stage"
+// buffer in the SAMPLER's HBM (exported over CUDA IPC) and the trainer pulls it with ONE peer copy over NVLink.
+// Tickets + per-entry semaphores follow the reference's queue (send_cnt / recv_cnt, sem_list / release_list).
+constexpr int kQueueDepth = 16, kStagePerSampler = 4;
+struct TaskDesc {
+  uint64_t key, epoch, bytes;
+  uint32_t num_layer, num_input, num_output, sampler, stage, stage_gen;
+  uint64_t num_src[XG_MAX_LAYERS], num_dst[XG_MAX_LAYERS], num_edge[XG_MAX_LAYERS];
+  // byte offsets inside the stage buffer; kNone = that array does not exist for this batch
+  uint64_t off_input, off_output, off_row[XG_MAX_LAYERS], off_col[XG_MAX_LAYERS], off_data[XG_MAX_LAYERS],
+      off_csc[XG_MAX_LAYERS];
+  double sample_time;
+};
+constexpr uint64_t kNone = ~0ull;
+struct TaskQueueBlock {
+  uint64_t send_cnt, recv_cnt;  // tickets (MQ_MetaData::Put/Get)
+  sem_t filled[kQueueDepth], vacant[kQueueDepth];
+  TaskDesc desc[kQueueDepth];
+  sem_t stage_free[kMaxWorker][kStagePerSampler];
+  unsigned char stage_ipc[kMaxWorker][kStagePerSampler][64];
+  uint32_t stage_gen[kMaxWorker][kStagePerSampler];  // bumped when a stage buffer is re-allocated (grown)
+  int num_sampler, num_trainer;
+};
+
 struct SharedBlock {
   pthread_barrier_t barrier;
   int num_worker;
@@ -404,8 +436,10 @@ struct BatchHolder {
   xg_batch *batch = nullptr;
   xg_batch_view view{};
   uint64_t key = 0;
+  std::function<void()> on_release;  // arch5 trainer: the landing buffers behind `view` go back to their pool
   ~BatchHolder() {
     if (batch) xg_batch_release(batch);
+    if (on_release) on_release();
   }
 };
 using BatchPtr = std::shared_ptr<BatchHolder>;
@@ -433,6 +467,15 @@ struct Engine {
   BatchPtr current;
   std::vector<std::thread> threads;
   bool producer_done = false;
+  // arch5
+  TaskQueueBlock *queue = nullptr;
+  int role = 0;  // 0 = sampler + trainer in one process (arch0-4, 6), 1 = arch5 sampler, 2 = arch5 trainer
+  struct Stage { void *ptr = nullptr; size_t cap = 0; } stages[kStagePerSampler];
+  unsigned next_stage = 0;
+  struct Landing { void *xfer = nullptr, *feat = nullptr; int64_t *label = nullptr; size_t cap_xfer = 0, cap_feat = 0, cap_label = 0; bool busy = false; };
+  std::vector<std::unique_ptr<Landing>> landings;
+  struct PeerStage { void *ptr = nullptr; uint32_t gen = 0; };
+  PeerStage peer_stage[kMaxWorker][kStagePerSampler];
   // SAMGRAPH_SANITY_CHECK (constant.cc:58, run_config.cc option_sanity_check)
   bool sanity_check = false;
   uint64_t *d_sanity = nullptr;
@@ -763,6 +806,8 @@ void sanity_check_batch(Engine &e, const xg_batch_view &v, size_t epoch) {
   SAM_CHECK_MSG(bad == 0, "SAMGRAPH_SANITY_CHECK: " + std::to_string(bad) + " violation(s) in batch " + std::to_string(v.key));
 }
 
+void send_task(Engine &e, const xg_batch_view &v, size_t epoch, double sample_time);
+
 bool produce_one(Engine &e) {
   SAM_CHECK_MSG(e.sampler_ready, "sample_init / init has not run");
   create_sampler(e);
@@ -801,9 +846,189 @@ bool produce_one(Engine &e) {
   g_prof.log_epoch_add(epoch, kLogEpochSampleTotalTime, t_total);
   g_prof.log_epoch_add(epoch, kLogEpochNumSample, edges);
   g_prof.log_epoch_add(epoch, kLogEpochFeatureBytes, feat_bytes);
+  if (e.role == 1) {  // arch5 sampler: the Task goes to a trainer process (RunArch5LoopsOnce / DoGPUSample + Send)
+    send_task(e, holder->view, epoch, t_total);
+    return true;       // holder dies here: the slot is free again, the payload lives in the stage buffer
+  }
   {
     std::lock_guard<std::mutex> lk(e.mu);
     e.pool.push_back(holder);  // GraphPool::Submit
+  }
+  e.cv.notify_all();
+  return true;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// arch5 task hand-over (see TaskQueueBlock).  Sampler side = MessageTaskQueue::Send (task_queue.cc:332-367), trainer side
+// = MessageTaskQueue::Recv + DoGPUFeatureExtract/DoGPULabelExtract... of RunArch5 extract loops (dist_loops_arch5.cc).
+bool sem_wait_or_shutdown(Engine &e, sem_t *sem) {
+  for (;;) {
+    timespec ts;
+    clock_gettime(CLOCK_REALTIME, &ts);
+    ts.tv_nsec += 50 * 1000 * 1000;
+    if (ts.tv_nsec >= 1000000000L) { ts.tv_sec += 1; ts.tv_nsec -= 1000000000L; }
+    if (sem_timedwait(sem, &ts) == 0) return true;
+    SAM_CHECK_MSG(errno == ETIMEDOUT || errno == EINTR, "sem_timedwait failed");
+    std::lock_guard<std::mutex> lk(e.mu);
+    if (e.shutdown) return false;
+  }
+}
+
+inline uint64_t align256(uint64_t x) { return (x + 255) & ~255ull; }
+
+void send_task(Engine &e, const xg_batch_view &v, size_t epoch, double sample_time) {
+  SAM_CHECK(e.queue != nullptr);
+  TaskQueueBlock &q = *e.queue;
+  const double t0 = now_s();
+  const int s = e.worker_id;
+  TaskDesc d;
+  std::memset(&d, 0, sizeof(d));
+  d.key = v.key; d.epoch = epoch; d.num_layer = v.num_layer; d.num_input = v.num_input; d.num_output = v.num_output;
+  d.sampler = (uint32_t)s; d.sample_time = sample_time;
+  // layout: input_nodes | output_nodes | per layer row | col | [data] | [csc_indptr], each 256-byte aligned
+  struct Piece { const void *src; uint64_t off, bytes; };
+  std::vector<Piece> pieces;
+  uint64_t at = 0;
+  auto place = [&](const void *src, uint64_t count) -> uint64_t {
+    if (src == nullptr) return kNone;
+    const uint64_t off = at;
+    pieces.push_back({src, off, count * sizeof(uint32_t)});
+    at = align256(at + count * sizeof(uint32_t));
+    return off;
+  };
+  d.off_input = place(v.input_nodes, v.num_input);
+  d.off_output = place(v.output_nodes, v.num_output);
+  for (uint32_t l = 0; l < v.num_layer; ++l) {
+    d.num_src[l] = v.num_src[l]; d.num_dst[l] = v.num_dst[l]; d.num_edge[l] = v.num_edge[l];
+    d.off_row[l] = place(v.row[l], v.num_edge[l]);
+    d.off_col[l] = place(v.col[l], v.num_edge[l]);
+    d.off_data[l] = place(v.data[l], v.num_edge[l]);
+    d.off_csc[l] = place(v.csc_indptr[l], v.num_dst[l] + 1);
+  }
+  d.bytes = std::max<uint64_t>(at, 256);
+  // a stage buffer of this sampler that no trainer is still pulling from
+  const unsigned k = e.next_stage++ % kStagePerSampler;
+  if (!sem_wait_or_shutdown(e, &q.stage_free[s][k])) return;
+  Engine::Stage &st = e.stages[k];
+  if (st.cap < d.bytes) {  // first use, or a batch larger than any before: (re)allocate with slack, export again
+    if (st.ptr) SAM_XG(xg_device_free(st.ptr));
+    st.cap = d.bytes + d.bytes / 4;
+    SAM_XG(xg_device_malloc(&st.ptr, st.cap));  // 2 MiB granular: peer reads of smaller blocks crawl
+    SAM_XG(xg_ipc_export(st.ptr, q.stage_ipc[s][k]));
+    __atomic_add_fetch(&q.stage_gen[s][k], 1u, __ATOMIC_SEQ_CST);
+  }
+  for (const Piece &p : pieces)
+    if (p.bytes)
+      SAM_CUDA(cudaMemcpyAsync(static_cast<char *>(st.ptr) + p.off, p.src, p.bytes, cudaMemcpyDeviceToDevice, e.stream));
+  SAM_CUDA(cudaStreamSynchronize(e.stream));
+  d.stage = k;
+  d.stage_gen = __atomic_load_n(&q.stage_gen[s][k], __ATOMIC_SEQ_CST);
+  const uint64_t ticket = __atomic_fetch_add(&q.send_cnt, 1ull, __ATOMIC_SEQ_CST);  // MQ_MetaData::Put
+  const int slot = (int)(ticket % kQueueDepth);
+  if (!sem_wait_or_shutdown(e, &q.vacant[slot])) return;  // ReleaseWait
+  q.desc[slot] = d;
+  SAM_CHECK(sem_post(&q.filled[slot]) == 0);  // SemPost
+  const double t_send = now_s() - t0;
+  g_prof.log_step(v.key, kLogL1SendTime, t_send, false);
+  g_prof.log_epoch_add(epoch, kLogEpochSampleSendTime, t_send);
+}
+
+Engine::Landing *acquire_landing(Engine &e) {
+  for (int spins = 0;; ++spins) {
+    {
+      std::lock_guard<std::mutex> lk(e.mu);
+      for (auto &l : e.landings)
+        if (!l->busy) { l->busy = true; return l.get(); }
+      if (e.landings.size() < 6) {  // same bound as the sampler's slots: current + pooled + held by caller tensors
+        e.landings.emplace_back(new Engine::Landing());
+        e.landings.back()->busy = true;
+        return e.landings.back().get();
+      }
+      if (e.shutdown) return nullptr;
+    }
+    SAM_CHECK_MSG(spins < 300000, "every landing buffer is still referenced by caller tensors");
+    std::this_thread::sleep_for(std::chrono::microseconds(100));
+  }
+}
+
+void grow(void **p, size_t *cap, size_t need) {
+  if (*cap >= need) return;
+  if (*p) SAM_XG(xg_device_free(*p));
+  *cap = need + need / 4;
+  SAM_XG(xg_device_malloc(p, *cap));
+}
+
+// one Task: dequeue -> peer copy of the packed topology -> feature + label gather on THIS (trainer) GPU -> GraphPool
+bool recv_task(Engine &e) {
+  SAM_CHECK_MSG(e.queue != nullptr && e.trainer_ready, "train_init has not run");
+  TaskQueueBlock &q = *e.queue;
+  const double t0 = now_s();
+  const uint64_t ticket = __atomic_fetch_add(&q.recv_cnt, 1ull, __ATOMIC_SEQ_CST);  // MQ_MetaData::Get
+  const int slot = (int)(ticket % kQueueDepth);
+  if (!sem_wait_or_shutdown(e, &q.filled[slot])) return false;  // SemWait
+  const TaskDesc d = q.desc[slot];
+  SAM_CHECK(sem_post(&q.vacant[slot]) == 0);  // the descriptor is copied: the ring entry is free (ReleasePost)
+  Engine::PeerStage &ps = e.peer_stage[d.sampler][d.stage];
+  if (ps.ptr == nullptr || ps.gen != d.stage_gen) {
+    if (ps.ptr) SAM_XG(xg_ipc_close(ps.ptr));
+    SAM_XG(xg_ipc_import(q.stage_ipc[d.sampler][d.stage], &ps.ptr));
+    ps.gen = d.stage_gen;
+  }
+  Engine::Landing *land = acquire_landing(e);
+  if (!land) return false;
+  const size_t row_bytes = e.ds.feat_row_bytes();
+  grow(&land->xfer, &land->cap_xfer, d.bytes);
+  grow(&land->feat, &land->cap_feat, std::max<size_t>((size_t)d.num_input * row_bytes, 256));
+  grow(reinterpret_cast<void **>(&land->label), &land->cap_label, std::max<size_t>((size_t)d.num_output * 8, 256));
+  // the whole packed Task in one copy, sampler HBM -> trainer HBM (NVLink when they are different GPUs)
+  SAM_CUDA(cudaMemcpyAsync(land->xfer, ps.ptr, d.bytes, cudaMemcpyDefault, e.stream));
+  SAM_CUDA(cudaStreamSynchronize(e.stream));
+  SAM_CHECK(sem_post(&q.stage_free[d.sampler][d.stage]) == 0);  // the sampler may overwrite its stage buffer now
+  const double t_recv = now_s() - t0;
+  auto at = [&](uint64_t off) -> const uint32_t * {
+    return off == kNone ? nullptr : reinterpret_cast<const uint32_t *>(static_cast<const char *>(land->xfer) + off);
+  };
+  auto holder = std::make_shared<BatchHolder>();
+  holder->key = d.key;
+  xg_batch_view &v = holder->view;
+  std::memset(&v, 0, sizeof(v));
+  v.key = d.key; v.num_layer = d.num_layer; v.num_input = d.num_input; v.num_output = d.num_output;
+  v.input_nodes = at(d.off_input);
+  v.output_nodes = at(d.off_output);
+  for (uint32_t l = 0; l < d.num_layer; ++l) {
+    v.num_src[l] = d.num_src[l]; v.num_dst[l] = d.num_dst[l]; v.num_edge[l] = d.num_edge[l];
+    v.row[l] = at(d.off_row[l]); v.col[l] = at(d.off_col[l]); v.data[l] = at(d.off_data[l]); v.csc_indptr[l] = at(d.off_csc[l]);
+  }
+  Engine *ep = &e;
+  holder->on_release = [ep, land] {
+    std::lock_guard<std::mutex> lk(ep->mu);
+    land->busy = false;
+  };
+  // DoGPUFeatureExtract / DoGPULabelExtract on the trainer GPU (dist/dist_loops.cc:843-974): one routed gather launch
+  const double t1 = now_s();
+  if (d.num_input) SAM_XG(xg_extract_ggms(&e.store, v.input_nodes, d.num_input, land->feat, nullptr, e.stream));
+  if (d.num_output) SAM_XG(xg_extract(land->label, e.d_label, v.output_nodes, d.num_output, 1, XG_I64, e.stream));
+  SAM_CUDA(cudaStreamSynchronize(e.stream));
+  v.input_feat = land->feat;
+  v.output_label = land->label;
+  const double t_copy = now_s() - t1;
+  double edges = 0;
+  for (uint32_t l = 0; l < d.num_layer; ++l) edges += (double)d.num_edge[l];
+  const double feat_bytes = (double)d.num_input * row_bytes;
+  g_prof.log_step(d.key, kLogL1NumSample, edges, false);
+  g_prof.log_step(d.key, kLogL1NumNode, (double)d.num_input, false);
+  g_prof.log_step(d.key, kLogL1SampleTime, d.sample_time, false);
+  g_prof.log_step(d.key, kLogL1RecvTime, t_recv, false);
+  g_prof.log_step(d.key, kLogL1CopyTime, t_copy, false);
+  g_prof.log_step(d.key, kLogL1FeatureBytes, feat_bytes, false);
+  g_prof.log_step(d.key, kLogL1LabelBytes, (double)d.num_output * 8, false);
+  g_prof.log_epoch_add(d.epoch, kLogEpochSampleTime, d.sample_time);
+  g_prof.log_epoch_add(d.epoch, kLogEpochCopyTime, t_recv + t_copy);
+  g_prof.log_epoch_add(d.epoch, kLogEpochNumSample, edges);
+  g_prof.log_epoch_add(d.epoch, kLogEpochFeatureBytes, feat_bytes);
+  {
+    std::lock_guard<std::mutex> lk(e.mu);
+    e.pool.push_back(holder);
   }
   e.cv.notify_all();
   return true;
@@ -950,13 +1175,21 @@ void samgraph_config(const char **keys, const char **vals, const size_t n) {
       if (c.sampler_device < 0) c.sampler_device = c.trainer_device;
       SAM_CHECK_MSG(c.sampler_device >= 0, "a CUDA context is required (xgnn_b200 has no CPU path)");
       break;
+    case kArch5:  // operation.cc:110-119: decoupled sampler / trainer processes
+      SAM_CHECK(m.count("num_sample_worker") && m.count("num_train_worker"));
+      c.num_worker = std::stoull(m["num_sample_worker"]);  // the train set is split over the SAMPLERS (dist_engine.cc:144-148)
+      c.num_train_worker = std::stoull(m["num_train_worker"]);
+      SAM_CHECK(c.num_worker >= 1 && c.num_worker <= (size_t)kMaxWorker);
+      SAM_CHECK(c.num_train_worker >= 1 && c.num_train_worker <= (size_t)kMaxWorker);
+      SAM_CHECK_MSG(!(m.count("have_switcher") && std::stoi(m["have_switcher"]) != 0), "arch5 switcher: out of scope");
+      break;
     case kArch6:
       SAM_CHECK(m.count("num_worker"));
       c.num_worker = std::stoull(m["num_worker"]);
       SAM_CHECK(c.num_worker >= 1 && c.num_worker <= (size_t)kMaxWorker);
       break;
     default:
-      fatal(__FILE__, __LINE__, "arch " + m["_arch"] + " is a different deployment mode (arch5/arch9): out of scope");
+      fatal(__FILE__, __LINE__, "arch " + m["_arch"] + " is a different deployment mode (arch9, UM sampler): out of scope");
   }
   if (c.sample_type != XG_RANDOM_WALK) {  // operation.cc:150-161
     SAM_CHECK(m.count("num_fanout") && m.count("fanout"));
@@ -1002,7 +1235,8 @@ void samgraph_config(const char **keys, const char **vals, const size_t n) {
 
 void samgraph_init(void) {  // operation.cc:328-334 (single process)
   SAM_CHECK(g_cfg.is_configured);
-  SAM_CHECK_MSG(g_cfg.run_arch != kArch6, "arch6 starts with samgraph_data_init (then fork, sample_init, train_init)");
+  SAM_CHECK_MSG(g_cfg.run_arch != kArch6 && g_cfg.run_arch != kArch5,
+                "arch5 / arch6 start with samgraph_data_init (then fork, sample_init, train_init)");
   create_engine(false);
   Engine &e = engine();
   common_device_init(e, g_cfg.sampler_device);
@@ -1014,6 +1248,20 @@ void samgraph_data_init(void) {  // operation.cc:509-533: parent process, BEFORE
   SAM_CHECK(g_cfg.is_configured);
   create_engine(true);
   Engine &e = engine();
+  if (g_cfg.run_arch == kArch5) {  // the task queue every sampler and trainer process inherits (MemoryQueue ctor, memory_queue.cc:32-40)
+    void *mem = ::mmap(nullptr, sizeof(TaskQueueBlock), PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+    SAM_CHECK(mem != MAP_FAILED);
+    std::memset(mem, 0, sizeof(TaskQueueBlock));
+    e.queue = static_cast<TaskQueueBlock *>(mem);
+    e.queue->num_sampler = (int)g_cfg.num_worker;
+    e.queue->num_trainer = (int)g_cfg.num_train_worker;
+    for (int i = 0; i < kQueueDepth; ++i) {
+      SAM_CHECK(sem_init(&e.queue->filled[i], 1, 0) == 0);  // sem_list
+      SAM_CHECK(sem_init(&e.queue->vacant[i], 1, 1) == 0);  // release_list
+    }
+    for (int w = 0; w < kMaxWorker; ++w)
+      for (int k = 0; k < kStagePerSampler; ++k) SAM_CHECK(sem_init(&e.queue->stage_free[w][k], 1, 1) == 0);
+  }
   if (g_cfg.run_arch == kArch6) {
     void *mem = ::mmap(nullptr, sizeof(SharedBlock), PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
     SAM_CHECK(mem != MAP_FAILED);
@@ -1048,7 +1296,12 @@ void samgraph_data_init(void) {  // operation.cc:509-533: parent process, BEFORE
 
 void samgraph_sample_init(int worker_id, const char *ctx) {  // operation.cc:535-540 -> DistEngine::SampleInit
   Engine &e = engine();
-  SAM_CHECK(g_cfg.run_arch == kArch6 && worker_id >= 0 && (size_t)worker_id < g_cfg.num_worker);
+  SAM_CHECK((g_cfg.run_arch == kArch6 || g_cfg.run_arch == kArch5) && worker_id >= 0 && (size_t)worker_id < g_cfg.num_worker);
+  if (g_cfg.run_arch == kArch5) {
+    SAM_CHECK_MSG(e.role == 0, "arch5: a process is either a sampler or a trainer");
+    SAM_CHECK_MSG(g_cfg.cache_policy != kCacheByPreSample, "arch5: presampled ranking needs the sampler in the trainer process");
+    e.role = 1;
+  }
   e.worker_id = worker_id;
   common_device_init(e, parse_ctx(ctx));
   sampler_side_init(e);
@@ -1056,6 +1309,15 @@ void samgraph_sample_init(int worker_id, const char *ctx) {  // operation.cc:535
 
 void samgraph_train_init(int worker_id, const char *ctx) {  // operation.cc:549-554 -> DistEngine::TrainInit
   Engine &e = engine();
+  if (g_cfg.run_arch == kArch5) {  // a trainer-only process on its own GPU: cache + labels, no topology
+    SAM_CHECK_MSG(e.role == 0, "arch5: a process is either a sampler or a trainer");
+    SAM_CHECK(worker_id >= 0 && (size_t)worker_id < g_cfg.num_train_worker);
+    e.role = 2;
+    e.worker_id = worker_id;
+    common_device_init(e, parse_ctx(ctx));
+    trainer_side_init(e);
+    return;
+  }
   SAM_CHECK(g_cfg.run_arch == kArch6 && worker_id == e.worker_id);
   SAM_CHECK_MSG(parse_ctx(ctx) == e.device, "arch6 samples and trains on the same GPU (dist_engine.cc:589-700)");
   trainer_side_init(e);
@@ -1066,9 +1328,25 @@ void samgraph_switch_init(int, const char *, double) { fatal(__FILE__, __LINE__,
 
 void samgraph_sample_once(void) {  // operation.cc:380
   Engine &e = engine();
+  if (e.role == 2) {  // arch5 trainer, not pipelined: one extract-loop iteration (multi_gpu/train_graphsage.py:293-296)
+    recv_task(e);
+    return;
+  }
   if (!produce_one(e)) {
     std::lock_guard<std::mutex> lk(e.mu);
     e.producer_done = true;
+  }
+}
+
+static void extract_loop(Engine *e, long count) {  // DistEngine::StartExtract (arch5 trainer): `count` Tasks off the queue
+  SAM_CUDA(cudaSetDevice(e->device));
+  for (long i = 0; i < count; ++i) {
+    {
+      std::unique_lock<std::mutex> lk(e->mu);
+      e->cv.wait(lk, [&] { return e->pool.size() < 2 || e->shutdown; });
+      if (e->shutdown) return;
+    }
+    if (!recv_task(*e)) break;
   }
 }
 
@@ -1095,6 +1373,11 @@ void samgraph_start(void) {  // operation.cc:336-345: background producer for ev
 
 void samgraph_extract_start(int count) {  // operation.cc:556-559 -> DistEngine::StartExtract
   Engine &e = engine();
+  if (e.role == 2) {
+    SAM_CHECK(e.trainer_ready && !e.shutdown);
+    e.threads.emplace_back(extract_loop, &e, (long)count);
+    return;
+  }
   SAM_CHECK(e.sampler_ready && !e.shutdown);
   e.threads.emplace_back(producer_loop, &e, (long)count);
 }
@@ -1129,6 +1412,19 @@ size_t samgraph_feat_dim(void) { return engine().ds.feat_dim; }
 
 void samgraph_shutdown(void) {  // operation.cc:397-403
   Engine &e = engine();
+  if (e.role == 1 && e.queue) {
+    // the payload of every Task this sampler sent lives in ITS HBM until a trainer has pulled it: do not let the
+    // process (and with it the IPC-exported stage buffers) go away earlier (the reference's scripts keep samplers
+    // alive with a run-end barrier, multi_gpu/train_graphsage.py:170-171)
+    for (int k = 0; k < kStagePerSampler; ++k) {
+      if (!e.stages[k].ptr) continue;
+      timespec ts;
+      clock_gettime(CLOCK_REALTIME, &ts);
+      ts.tv_sec += 120;
+      if (sem_timedwait(&e.queue->stage_free[e.worker_id][k], &ts) != 0)
+        std::fprintf(stderr, "[samgraph] sampler %d: stage %d was never pulled by a trainer\n", e.worker_id, k);
+    }
+  }
   {
     std::lock_guard<std::mutex> lk(e.mu);
     e.shutdown = true;
