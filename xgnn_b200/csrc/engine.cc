@@ -476,6 +476,7 @@ struct Engine {
   std::vector<std::unique_ptr<Landing>> landings;
   struct PeerStage { void *ptr = nullptr; uint32_t gen = 0; };
   PeerStage peer_stage[kMaxWorker][kStagePerSampler];
+  cudaStream_t copy_stream = nullptr;  // arch5 trainer: Task k+1's peer copy, under Task k's gather
   // SAMGRAPH_SANITY_CHECK (constant.cc:58, run_config.cc option_sanity_check)
   bool sanity_check = false;
   uint64_t *d_sanity = nullptr;
@@ -939,7 +940,7 @@ Engine::Landing *acquire_landing(Engine &e) {
       std::lock_guard<std::mutex> lk(e.mu);
       for (auto &l : e.landings)
         if (!l->busy) { l->busy = true; return l.get(); }
-      if (e.landings.size() < 6) {  // same bound as the sampler's slots: current + pooled + held by caller tensors
+      if (e.landings.size() < 8) {  // current + 2 pooled + 2 in the extract thread + a few held by caller tensors
         e.landings.emplace_back(new Engine::Landing());
         e.landings.back()->busy = true;
         return e.landings.back().get();
@@ -958,14 +959,24 @@ void grow(void **p, size_t *cap, size_t need) {
   SAM_XG(xg_device_malloc(p, *cap));
 }
 
-// one Task: dequeue -> peer copy of the packed topology -> feature + label gather on THIS (trainer) GPU -> GraphPool
-bool recv_task(Engine &e) {
+// one Task: dequeue -> peer copy of the packed topology -> feature + label gather on THIS (trainer) GPU -> GraphPool.
+// Two halves, so that the extract thread can have Task k+1's peer copy in flight (copy stream) while Task k's rows
+// are being gathered (engine stream).
+struct PendingTask {
+  TaskDesc d;
+  Engine::Landing *land = nullptr;
+  cudaEvent_t copied = nullptr;
+  double t0 = 0;
+  bool prefetched = false;  // begun while the previous Task was still being gathered
+};
+
+std::unique_ptr<PendingTask> recv_begin(Engine &e) {
   SAM_CHECK_MSG(e.queue != nullptr && e.trainer_ready, "train_init has not run");
   TaskQueueBlock &q = *e.queue;
   const double t0 = now_s();
   const uint64_t ticket = __atomic_fetch_add(&q.recv_cnt, 1ull, __ATOMIC_SEQ_CST);  // MQ_MetaData::Get
   const int slot = (int)(ticket % kQueueDepth);
-  if (!sem_wait_or_shutdown(e, &q.filled[slot])) return false;  // SemWait
+  if (!sem_wait_or_shutdown(e, &q.filled[slot])) return nullptr;  // SemWait
   const TaskDesc d = q.desc[slot];
   SAM_CHECK(sem_post(&q.vacant[slot]) == 0);  // the descriptor is copied: the ring entry is free (ReleasePost)
   Engine::PeerStage &ps = e.peer_stage[d.sampler][d.stage];
@@ -975,16 +986,33 @@ bool recv_task(Engine &e) {
     ps.gen = d.stage_gen;
   }
   Engine::Landing *land = acquire_landing(e);
-  if (!land) return false;
+  if (!land) return nullptr;
   const size_t row_bytes = e.ds.feat_row_bytes();
   grow(&land->xfer, &land->cap_xfer, d.bytes);
   grow(&land->feat, &land->cap_feat, std::max<size_t>((size_t)d.num_input * row_bytes, 256));
   grow(reinterpret_cast<void **>(&land->label), &land->cap_label, std::max<size_t>((size_t)d.num_output * 8, 256));
+  if (!e.copy_stream) SAM_CUDA(cudaStreamCreateWithFlags(&e.copy_stream, cudaStreamNonBlocking));
+  std::unique_ptr<PendingTask> p(new PendingTask());
+  p->d = d; p->land = land; p->t0 = t0;
+  SAM_CUDA(cudaEventCreateWithFlags(&p->copied, cudaEventDisableTiming));
   // the whole packed Task in one copy, sampler HBM -> trainer HBM (NVLink when they are different GPUs)
-  SAM_CUDA(cudaMemcpyAsync(land->xfer, ps.ptr, d.bytes, cudaMemcpyDefault, e.stream));
-  SAM_CUDA(cudaStreamSynchronize(e.stream));
+  SAM_CUDA(cudaMemcpyAsync(land->xfer, ps.ptr, d.bytes, cudaMemcpyDefault, e.copy_stream));
+  SAM_CUDA(cudaEventRecord(p->copied, e.copy_stream));
+  return p;
+}
+
+bool recv_finish(Engine &e, std::unique_ptr<PendingTask> p) {
+  if (!p) return false;
+  TaskQueueBlock &q = *e.queue;
+  const TaskDesc &d = p->d;
+  Engine::Landing *land = p->land;
+  const size_t row_bytes = e.ds.feat_row_bytes();
+  const double t_wait = now_s();
+  SAM_CUDA(cudaEventSynchronize(p->copied));
+  SAM_CUDA(cudaEventDestroy(p->copied));
   SAM_CHECK(sem_post(&q.stage_free[d.sampler][d.stage]) == 0);  // the sampler may overwrite its stage buffer now
-  const double t_recv = now_s() - t0;
+  // time this Task kept the trainer waiting (dequeue + copy when nothing overlapped it, ~0 when prefetched)
+  const double t_recv = p->prefetched ? now_s() - t_wait : now_s() - p->t0;
   auto at = [&](uint64_t off) -> const uint32_t * {
     return off == kNone ? nullptr : reinterpret_cast<const uint32_t *>(static_cast<const char *>(land->xfer) + off);
   };
@@ -1033,6 +1061,8 @@ bool recv_task(Engine &e) {
   e.cv.notify_all();
   return true;
 }
+
+bool recv_task(Engine &e) { return recv_finish(e, recv_begin(e)); }
 
 void common_device_init(Engine &e, int device) {
   e.device = device;
@@ -1340,13 +1370,20 @@ void samgraph_sample_once(void) {  // operation.cc:380
 
 static void extract_loop(Engine *e, long count) {  // DistEngine::StartExtract (arch5 trainer): `count` Tasks off the queue
   SAM_CUDA(cudaSetDevice(e->device));
+  std::unique_ptr<PendingTask> next;
   for (long i = 0; i < count; ++i) {
     {
       std::unique_lock<std::mutex> lk(e->mu);
       e->cv.wait(lk, [&] { return e->pool.size() < 2 || e->shutdown; });
       if (e->shutdown) return;
     }
-    if (!recv_task(*e)) break;
+    if (!next) next = recv_begin(*e);
+    std::unique_ptr<PendingTask> cur = std::move(next);
+    if (i + 1 < count) {  // Task i+1 crosses NVLink while Task i's rows are gathered
+      next = recv_begin(*e);
+      if (next) next->prefetched = true;
+    }
+    if (!recv_finish(*e, std::move(cur))) break;
   }
 }
 
