@@ -365,7 +365,9 @@ def run_xgnn(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     V, E, dim, dtype, ncls, frac = D.SHAPES[args.shape]
     t_build = time.perf_counter()
-    st = D.build_store(args.shape, local, rank, world, scale=args.scale, replicate_pct=args.replicate)
+    st = D.build_store(args.shape, local, rank, world, scale=args.scale, replicate_pct=args.replicate,
+                       replica_words=os.environ.get("XG_BENCH_REPLICA_WORDS", "1") != "0",
+                       flat_when_full=os.environ.get("XG_BENCH_FORCE_TABLE", "0") == "0")  # 1: the N > 1 lookup path on one GPU
     if world > 1:
         ptrs = exchange_parts(st, dist, torch)
         D.attach(st, ptrs["indptr"], ptrs["indices"], ptrs["feat_part"])

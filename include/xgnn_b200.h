@@ -96,6 +96,9 @@ typedef struct xg_feature_store {
   uint32_t compact_bitwidth; /* 0: rank routing above.  b > 0 (needs num_replicated == 0): a cache_table value is
                               * (part << (32 - b)) | row, the ICS'22 clique placement's compact map
                               * (cuda/ics22_song_dist_feature.h:38-47, cuda_cache_manager_host.cc:203-222) */
+  const void *replica_words; /* optional accelerator for the replicated tier, or NULL: uint2[ceil(num_node / 32)] from
+                              * xg_build_replica_words.  Needs the replica laid out by node id
+                              * (cache_table[v] = number of replicated nodes with a smaller id). */
 } xg_feature_store;
 
 /* ------------------------------------------------------------------------------------------------
@@ -318,6 +321,13 @@ size_t xg_predict_num_nodes(size_t batch_size, const uint32_t *fanout, size_t nu
 /* std::shuffle(nodes, nodes + n, std::mt19937(n)): the cache-rank order of GPUCacheManager,
  * cuda/cuda_cache_manager_host.cc:162-171 (same libstdc++ algorithm, hence the same order). */
 int xg_shuffle_cache_ranks(uint32_t *h_nodes, size_t num_cached);
+/* Rank/select words of the replicated tier: word w = { bit i: node 32w+i is replicated (cache_table < num_replicated),
+ * number of replicated nodes with id < 32w }.  8 B per 32 nodes, so L2-resident where the 4 B x V table is not: the
+ * gather resolves replicated nodes from these words alone and only reads the table for the rest.  Fails with
+ * XG_ERR_INVALID when the replica is not in node-id order.  Init-time (allocates scratch, synchronises `stream`). */
+int xg_build_replica_words(const uint32_t *d_cache_table, uint32_t num_node, uint32_t num_replicated, void *d_words,
+                           void *stream);
+
 /* ICS'22 clique feature placement (comparison baseline): ICS22SongPlacementSolver, cuda/ics22_song_dist_feature.cc:22-167,
  * seen from ONE worker.  h_rank_nodes / h_rank_weight: all nodes by weight descending (ties: node id descending) and
  * their weights - the reference uses the in-degree (ics22_song_dist_feature.cc:196-213); xg_presample_accumulate over

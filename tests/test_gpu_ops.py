@@ -414,3 +414,48 @@ def test_extract_through_ics22_compact_map(num_dev, clique, alpha, pct):
         ops.GPUExtractMissData(out2, host, gms, gmd, dim * 4)
         ops.CombineCacheData(out2, st, gcs, gcd)
         assert np.array_equal(out2.cpu().numpy().view(np.uint32), want.view(np.uint32))
+
+
+@pytest.mark.parametrize("P,pct,rep", [(1, 0.5, 0.2), (4, 0.8, 0.3), (8, 1.0, 0.6), (2, 0.3, 0.3)])
+def test_extract_two_tier_rank_select_words(P, pct, rep):
+    """Replicated tier laid out by node id and resolved through the rank/select words (xg_build_replica_words) instead of
+    the direct-address table: the words must reproduce the table for every replicated node, the gather must return
+    CPUExtract's rows bit for bit, and a replica that is NOT in node-id order must be refused."""
+    from xgnn_b200 import ops
+    from xgnn_b200._clib import lib
+    V, dim = 30011, 100
+    feat = synth.make_features(V, dim)
+    indptr, _ = synth.make_graph(V, 200000, seed=5)
+    rank = synth.degree_rank(indptr).copy()
+    ncached, nrep = int(V * pct), int(V * rep)
+    policy_table = O.build_cache_table(rank, ncached, V)
+    rank[:nrep] = np.sort(rank[:nrep])
+    table = O.build_cache_table(rank, ncached, V)
+    replica, parts = O.hybrid_placement(feat, rank, ncached, nrep, P)
+    d_table = dev(table)
+    words = ops.build_replica_words(d_table, nrep)
+    w = words.cpu().numpy().view(np.uint32)
+    member = np.zeros(((V + 31) // 32) * 32, bool)
+    member[:V] = table < nrep
+    bits = np.packbits(member.reshape(-1, 32), axis=1, bitorder="little").view(np.uint32).reshape(-1)
+    assert np.array_equal(w[:, 0], bits)
+    pc = member.reshape(-1, 32).sum(1)
+    assert np.array_equal(w[:, 1], np.concatenate([[0], np.cumsum(pc)[:-1]]).astype(np.uint32))
+    d_parts = [dev(p) if len(p) else torch.zeros((1, dim), device="cuda") for p in parts]
+    h_feat = torch.from_numpy(feat).pin_memory()
+    store = ops.make_feature_store(dim * 4, h_feat, d_table, d_parts, local_parts=(0,), replica=dev(replica),
+                                   num_replicated=nrep, replica_words=words)
+    nodes = np.random.default_rng(12).integers(0, V, size=20011).astype(np.uint32)
+    stats = torch.zeros(4, dtype=torch.int64, device="cuda")
+    out = ops.ExtractGGMS(store, dev(nodes), dim, torch.float32, stats=stats)
+    out_ring = ops.ExtractGGMS(store, dev(nodes), dim, torch.float32)
+    want = O.extract(feat, nodes)
+    assert np.array_equal(host(out).view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(host(out_ring).view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(O.extract_hybrid(feat, nodes, table, replica, parts).view(np.uint32), want.view(np.uint32))
+    r = table[nodes]
+    st = stats.cpu().numpy()
+    assert st[2] == (r == 0xFFFFFFFF).sum() and st[0] + st[1] == (r != 0xFFFFFFFF).sum()
+    if nrep > 1 and not np.array_equal(policy_table, table):
+        bad = torch.empty_like(words)
+        assert lib.xg_build_replica_words(dev(policy_table).data_ptr(), V, nrep, bad.data_ptr(), None) != 0

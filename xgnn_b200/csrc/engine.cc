@@ -633,6 +633,7 @@ void build_feature_store(Engine &e) {
   // hottest ranks keep the policy order and are replicated per GPU; only the sharded remainder is shuffled
   size_t n_rep = parted ? (size_t)(V * cfg.replicate_percentage) : 0;
   if (n_rep > n_cached) n_rep = n_cached;
+  std::sort(ranks.begin(), ranks.begin() + n_rep);  // replicated tier by node id: resolved by rank/select (replica_words)
   if (parted && n_cached > n_rep)
     SAM_XG(xg_shuffle_cache_ranks(ranks.data() + n_rep, n_cached - n_rep));  // cuda_cache_manager_host.cc:162-171
   if (!ics22) {
@@ -714,6 +715,9 @@ void build_feature_store(Engine &e) {
   if (n_rep) {
     e.store.replica = gather_rows_to_device(ranks.data(), n_rep);
     e.store.num_replicated = (uint32_t)n_rep;
+    void *words = dev_alloc(e, ((V + 31) / 32) * 8);
+    SAM_XG(xg_build_replica_words(e.store.cache_table, (uint32_t)V, (uint32_t)n_rep, words, e.stream));
+    e.store.replica_words = words;
   }
   const int w = e.worker_id;
   std::vector<void *> mine(P, nullptr);

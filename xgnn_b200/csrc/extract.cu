@@ -15,6 +15,8 @@
 // Local HBM, NVLink-peer HBM and pinned host rows take the same path; only the pointer differs.
 #include "extract.cuh"
 
+#include <cub/cub.cuh>
+
 #include <cstdlib>
 
 namespace xg {
@@ -66,6 +68,20 @@ template <> __device__ __forceinline__ void st_stream<int4>(int4 *p, const int4 
                "r"(v.z), "r"(v.w) : "memory");
 }
 
+// node id -> cache-table value.  With `replica_words` (one {membership bits, exclusive popcount} pair per 32 node ids, 8 B x V / 32:
+// 28 MB for 111 M nodes, i.e. L2-resident, where the 4 B x V table is not and costs one 128-byte DRAM line per lookup)
+// a node of the replicated tier gets its row by rank/select without touching the table; everything else falls through
+// to the table.  The replica is laid out by node id, so select == table value (checked when the words are built).
+__device__ __forceinline__ uint32_t lookup_rank(const xg_feature_store &st, uint32_t idx) {
+  if (st.replica_words != nullptr) {
+    // default L2 priority; the rows themselves stream through with evict_first, so the words stay resident
+    const uint2 w = __ldg(reinterpret_cast<const uint2 *>(st.replica_words) + (idx >> 5));
+    const uint32_t bit = idx & 31u;
+    if ((w.x >> bit) & 1u) return w.y + __popc(w.x & ((1u << bit) - 1u));
+  }
+  return __ldg(st.cache_table + idx);
+}
+
 // cache-table value -> (part, row).  Default: DeviceDistFeature::Get (cuda/dist_graph.h:203-207), part r % P, row r / P.
 // compact_bitwidth != 0: DeviceICS22SongDistFeature::_GetRealPartId (cuda/ics22_song_dist_feature.h:38-47), the value
 // carries the owning GPU in its top bits and the row in the rest.
@@ -84,7 +100,7 @@ __device__ __forceinline__ const char *route_row(const xg_feature_store &st, int
                                                  int *klass) {
   uint32_t rank = kEmpty;
   if (mode == kCacheRank) rank = idx;
-  else if (mode == kByNode && st.cache_table != nullptr) rank = __ldg(st.cache_table + idx);
+  else if (mode == kByNode && st.cache_table != nullptr) rank = lookup_rank(st, idx);
   if (rank == kEmpty) {
     *klass = 2;  // host (or the flat table when nothing is cached)
     return static_cast<const char *>(st.host) + (size_t)idx * st.row_bytes;
@@ -132,7 +148,7 @@ gather_rows_kernel(const xg_feature_store st, int mode, const uint32_t *__restri
     const uint32_t r = g * 32 + lane;
     if (r < num_rows) {
       idx_cur = src_idx[r];
-      if (by_table) rank_cur = __ldg(st.cache_table + idx_cur);
+      if (by_table) rank_cur = lookup_rank(st, idx_cur);
     }
     const uint64_t rn = (uint64_t)(g + num_warps) * 32 + lane;
     if (rn < num_rows) idx_nxt = src_idx[rn];
@@ -144,7 +160,7 @@ gather_rows_kernel(const xg_feature_store st, int mode, const uint32_t *__restri
     uint32_t rank_nxt = kEmpty, idx_nn = 0;
     {
       const uint64_t rn = (uint64_t)(g + num_warps) * 32 + lane;
-      if (by_table && rn < num_rows) rank_nxt = __ldg(st.cache_table + idx_nxt);
+      if (by_table && rn < num_rows) rank_nxt = lookup_rank(st, idx_nxt);
       const uint64_t rnn = ((uint64_t)g + 2ull * num_warps) * 32 + lane;
       if (rnn < num_rows) idx_nn = src_idx[rnn];
     }
@@ -286,12 +302,12 @@ gather_rows_ring_kernel(const xg_feature_store st, int mode, const uint32_t *__r
     const uint32_t r = warp * 32 + lane;
     if (r < num_rows) {
       idx_cur = src_idx[r];
-      if (by_table) rank_cur = __ldg(st.cache_table + idx_cur);
+      if (by_table) rank_cur = lookup_rank(st, idx_cur);
     }
     const uint64_t rn = (uint64_t)(warp + num_warps) * 32 + lane;
     if (rn < num_rows) {
       idx_nxt = src_idx[rn];
-      if (by_table) rank_nxt = __ldg(st.cache_table + idx_nxt);
+      if (by_table) rank_nxt = lookup_rank(st, idx_nxt);
     }
   }
   const char *sp = lane < is.rows ? route(idx_cur, rank_cur) : nullptr;
@@ -332,7 +348,7 @@ gather_rows_ring_kernel(const xg_feature_store st, int mode, const uint32_t *__r
           rank_nxt = kEmpty;
           if (rn < num_rows) {
             idx_nxt = src_idx[rn];
-            if (by_table) rank_nxt = __ldg(st.cache_table + idx_nxt);
+            if (by_table) rank_nxt = lookup_rank(st, idx_nxt);
           }
         }
       }
@@ -643,3 +659,74 @@ int xg_get_miss_cache_index(const uint32_t *d_cache_table, const uint32_t *d_nod
 }
 
 }  // extern "C"
+
+// ---- rank/select words of the replicated tier ------------------------------------------------------
+namespace xg {
+namespace {
+
+__global__ void __launch_bounds__(256)
+replica_bits_kernel(const uint32_t *__restrict__ table, uint32_t num_node, uint32_t num_replicated, uint32_t *bits,
+                    uint32_t *counts, uint32_t num_words) {
+  const uint32_t lane = threadIdx.x & 31;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < num_words; w += (gridDim.x * blockDim.x) >> 5) {
+    const uint32_t v = w * 32 + lane;
+    const bool in = v < num_node && table[v] < num_replicated;
+    const uint32_t b = __ballot_sync(0xFFFFFFFFu, in);
+    if (lane == 0) {
+      bits[w] = b;
+      counts[w] = __popc(b);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+replica_words_kernel(const uint32_t *__restrict__ table, uint32_t num_node, const uint32_t *__restrict__ bits,
+                     const uint32_t *__restrict__ prefix, uint2 *words, uint32_t num_words, unsigned long long *mismatch) {
+  const uint32_t lane = threadIdx.x & 31;
+  for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < num_words; w += (gridDim.x * blockDim.x) >> 5) {
+    const uint32_t b = bits[w], p = prefix[w], v = w * 32 + lane;
+    if (lane == 0) words[w] = make_uint2(b, p);
+    // select must reproduce the table: the replicated tier has to be laid out by node id
+    if (((b >> lane) & 1u) && table[v] != p + __popc(b & ((1u << lane) - 1u))) atomicAdd(mismatch, 1ull);
+  }
+}
+
+}  // namespace
+}  // namespace xg
+
+extern "C" int xg_build_replica_words(const uint32_t *d_cache_table, uint32_t num_node, uint32_t num_replicated,
+                                      void *d_words, void *stream) {
+  XG_REQUIRE(d_cache_table && d_words, "NULL argument");
+  if (num_node == 0) return XG_OK;
+  cudaStream_t s = as_stream(stream);
+  const uint32_t num_words = (num_node + 31) / 32;
+  uint32_t *bits = nullptr, *counts = nullptr, *prefix = nullptr;
+  unsigned long long *mismatch = nullptr, h_mismatch = 0;
+  void *temp = nullptr;
+  size_t temp_bytes = 0;
+  XG_CUDA(cudaMalloc(&bits, (size_t)num_words * 3 * sizeof(uint32_t) + sizeof(unsigned long long) * 2));
+  counts = bits + num_words;
+  prefix = counts + num_words;
+  mismatch = reinterpret_cast<unsigned long long *>(bits + (size_t)((num_words * 3 + 1) & ~1u));
+  cudaError_t e = cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, counts, prefix, (int)num_words, s);
+  if (e == cudaSuccess) e = cudaMalloc(&temp, temp_bytes ? temp_bytes : 16);
+  if (e == cudaSuccess) e = cudaMemsetAsync(mismatch, 0, sizeof(unsigned long long), s);
+  if (e == cudaSuccess) {
+    const unsigned grid = grid_for(((size_t)num_words * 32 + 255) / 256, 8);
+    replica_bits_kernel<<<grid, 256, 0, s>>>(d_cache_table, num_node, num_replicated, bits, counts, num_words);
+    XG_LAUNCHED();
+    e = cub::DeviceScan::ExclusiveSum(temp, temp_bytes, counts, prefix, (int)num_words, s);
+    if (e == cudaSuccess) {
+      replica_words_kernel<<<grid, 256, 0, s>>>(d_cache_table, num_node, bits, prefix, static_cast<uint2 *>(d_words), num_words,
+                                                mismatch);
+      XG_LAUNCHED();
+      e = cudaMemcpyAsync(&h_mismatch, mismatch, sizeof(h_mismatch), cudaMemcpyDeviceToHost, s);
+      if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+    }
+  }
+  cudaFree(temp);
+  cudaFree(bits);
+  XG_CUDA(e);
+  XG_REQUIRE(h_mismatch == 0, "the replicated tier is not laid out by node id (cache_table[v] != rank of v among replicated nodes)");
+  return XG_OK;
+}

@@ -109,7 +109,7 @@ def cache_rank_nodes(num_node: int, num_cached: int, num_replicated: int = 0) ->
 
 def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale: int = 1, cache_pct: float = 1.0,
                 replicate_pct: float = 0.0, with_features: bool = True, seed: int = SYNTH_SEED,
-                flat_when_full: bool = True) -> GGMSStore:
+                flat_when_full: bool = True, replica_words: bool = True) -> GGMSStore:
     """Generate THIS rank's shards (topology part `rank`, feature part `rank`) of the named shape,
     scaled down by `scale`. Peer parts are attached afterwards (attach_peers) from IPC handles."""
     V, E, dim, dtype, num_class, train_frac = SHAPES[shape]
@@ -133,8 +133,9 @@ def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale
             st.local["flat"] = True
         elif with_features:
             n_cached = int(V * cache_pct)
-            n_rep = min(n_cached, int(V * replicate_pct)) if P > 1 else 0
+            n_rep = min(n_cached, int(V * replicate_pct)) if (P > 1 or not flat_when_full) else 0
             ranks = cache_rank_nodes(V, n_cached, n_rep)
+            ranks[:n_rep].sort()  # the replicated tier is stored by node id: its rows resolve by rank/select (replica_words)
             table = np.full(V, 0xFFFFFFFF, np.uint32)
             table[ranks] = np.arange(n_cached, dtype=np.uint32)
             st.local["cache_table"] = torch.from_numpy(table.view(np.int32)).to(dev)
@@ -146,6 +147,8 @@ def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale
                 hot = torch.from_numpy(np.ascontiguousarray(ranks[:n_rep]).view(np.int32)).to(dev)
                 st.local["replica"] = gen_features(n_rep, dim, dtype, dev, row_ids=hot)
                 del hot
+                if replica_words:
+                    st.local["replica_words"] = ops.build_replica_words(st.local["cache_table"], n_rep)
             del mine
         torch.cuda.synchronize()
     st.train = train_set(V, max(1, int(V * train_frac)))
@@ -167,5 +170,6 @@ def attach(st: GGMSStore, part_indptr=None, part_indices=None, feat_parts=None, 
     elif st.local.get("cache_table") is not None:
         st.store = ops.make_feature_store(st.row_bytes, host_feat, st.local["cache_table"], parts=feat_parts,
                                           local_parts=(st.rank,), replica=st.local.get("replica"),
-                                          num_replicated=st.local.get("num_replicated", 0))
+                                          num_replicated=st.local.get("num_replicated", 0),
+                                          replica_words=st.local.get("replica_words"))
     return st

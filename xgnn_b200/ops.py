@@ -209,7 +209,7 @@ def GPUExtract(src: torch.Tensor | int, index: torch.Tensor, dim: int | None = N
 
 def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_table: torch.Tensor | None = None,
                        parts=None, local_parts=(), replica=None, num_replicated: int = 0,
-                       compact_bitwidth: int = 0) -> XgFeatureStore:
+                       compact_bitwidth: int = 0, replica_words: torch.Tensor | None = None) -> XgFeatureStore:
     """DeviceDistFeature + cache table + host table in one handle (cuda/dist_graph.h:182-213)."""
     st = XgFeatureStore()
 
@@ -232,7 +232,8 @@ def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_ta
     st.num_replicated = num_replicated if replica is not None else 0
     assert not (compact_bitwidth and st.num_replicated), "the compact (ICS'22) map has no replicated tier of its own"
     st.compact_bitwidth = compact_bitwidth
-    st._keep = [host, cache_table, parts, replica]  # raw pointers inside: keep the tensors alive
+    st.replica_words = p(replica_words) if (replica_words is not None and st.num_replicated) else None
+    st._keep = [host, cache_table, parts, replica, replica_words]  # raw pointers inside: keep the tensors alive
     return st
 
 
@@ -452,6 +453,15 @@ def presample_rank(sampler: "MinibatchSampler", num_node: int, batches, key0: in
     rank_freq = torch.empty(num_node, dtype=torch.int32, device=sampler.device)
     check(lib.xg_presample_rank(_ptr(freq), num_node, _ptr(rank_nodes), _ptr(rank_freq), _stream()))
     return rank_nodes, rank_freq
+
+
+def build_replica_words(cache_table: torch.Tensor, num_replicated: int) -> torch.Tensor:
+    """rank/select words of the replicated tier (xg_build_replica_words): int32[ceil(V / 32), 2] = {bits, prefix}.
+    Raises when the replica is not laid out by node id."""
+    V = cache_table.numel()
+    words = torch.empty(((V + 31) // 32, 2), dtype=torch.int32, device=cache_table.device)
+    check(lib.xg_build_replica_words(_ptr(cache_table), V, num_replicated, _ptr(words), _stream()))
+    return words
 
 
 def sanity_check_ids(ids: torch.Tensor, num_node: int, epoch_map: torch.Tensor | None = None) -> int:
