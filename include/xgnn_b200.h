@@ -99,6 +99,10 @@ typedef struct xg_feature_store {
   const void *replica_words; /* optional accelerator for the replicated tier, or NULL: uint2[ceil(num_node / 32)] from
                               * xg_build_replica_words.  Needs the replica laid out by node id
                               * (cache_table[v] = number of replicated nodes with a smaller id). */
+  uint32_t replica_words_cover_all; /* 1 (as reported by xg_build_replica_words): every node is cached and the sharded tier is
+                                     * in node-id order as well, cache_table[v] = num_replicated + number of NON-replicated
+                                     * nodes with a smaller id - then no lookup reads the table at all */
+  uint32_t reserved;
 } xg_feature_store;
 
 /* ------------------------------------------------------------------------------------------------
@@ -324,9 +328,11 @@ int xg_shuffle_cache_ranks(uint32_t *h_nodes, size_t num_cached);
 /* Rank/select words of the replicated tier: word w = { bit i: node 32w+i is replicated (cache_table < num_replicated),
  * number of replicated nodes with id < 32w }.  8 B per 32 nodes, so L2-resident where the 4 B x V table is not: the
  * gather resolves replicated nodes from these words alone and only reads the table for the rest.  Fails with
- * XG_ERR_INVALID when the replica is not in node-id order.  Init-time (allocates scratch, synchronises `stream`). */
+ * XG_ERR_INVALID when the replica is not in node-id order.  *h_cover_all (optional) = 1 when, in addition, every node is
+ * cached and the sharded tier is in node-id order too (see xg_feature_store.replica_words_cover_all).
+ * Init-time (allocates scratch, synchronises `stream`). */
 int xg_build_replica_words(const uint32_t *d_cache_table, uint32_t num_node, uint32_t num_replicated, void *d_words,
-                           void *stream);
+                           uint32_t *h_cover_all, void *stream);
 
 /* ICS'22 clique feature placement (comparison baseline): ICS22SongPlacementSolver, cuda/ics22_song_dist_feature.cc:22-167,
  * seen from ONE worker.  h_rank_nodes / h_rank_weight: all nodes by weight descending (ties: node id descending) and

@@ -430,10 +430,13 @@ def test_extract_two_tier_rank_select_words(P, pct, rep):
     ncached, nrep = int(V * pct), int(V * rep)
     policy_table = O.build_cache_table(rank, ncached, V)
     rank[:nrep] = np.sort(rank[:nrep])
+    if pct == 1.0:
+        rank[nrep:] = np.sort(rank[nrep:])  # everything cached, sharded tier by node id too: the words cover every node
     table = O.build_cache_table(rank, ncached, V)
     replica, parts = O.hybrid_placement(feat, rank, ncached, nrep, P)
     d_table = dev(table)
     words = ops.build_replica_words(d_table, nrep)
+    assert words.cover_all == (pct == 1.0)
     w = words.cpu().numpy().view(np.uint32)
     member = np.zeros(((V + 31) // 32) * 32, bool)
     member[:V] = table < nrep
@@ -456,6 +459,11 @@ def test_extract_two_tier_rank_select_words(P, pct, rep):
     r = table[nodes]
     st = stats.cpu().numpy()
     assert st[2] == (r == 0xFFFFFFFF).sum() and st[0] + st[1] == (r != 0xFFFFFFFF).sum()
+    if words.cover_all:
+        # the table is never read in this mode: a poisoned one (every node -> replica row 0) must not change a single byte
+        poisoned = ops.make_feature_store(dim * 4, h_feat, torch.zeros_like(d_table), d_parts, local_parts=(0,),
+                                          replica=dev(replica), num_replicated=nrep, replica_words=words)
+        assert np.array_equal(host(ops.ExtractGGMS(poisoned, dev(nodes), dim, torch.float32)).view(np.uint32), want.view(np.uint32))
     if nrep > 1 and not np.array_equal(policy_table, table):
         bad = torch.empty_like(words)
-        assert lib.xg_build_replica_words(dev(policy_table).data_ptr(), V, nrep, bad.data_ptr(), None) != 0
+        assert lib.xg_build_replica_words(dev(policy_table).data_ptr(), V, nrep, bad.data_ptr(), None, None) != 0

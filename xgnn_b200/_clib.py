@@ -40,6 +40,8 @@ class XgFeatureStore(Structure):
         ("num_replicated", c_uint32),
         ("compact_bitwidth", c_uint32),
         ("replica_words", c_void_p),
+        ("replica_words_cover_all", c_uint32),
+        ("reserved", c_uint32),
     ]
 
 
@@ -157,7 +159,7 @@ _sig("xg_sampler_destroy", c_int, c_void_p)
 _sig("xg_sampler_submit", c_int, c_void_p, c_void_p, c_size_t, c_int, c_uint64, POINTER(c_void_p))
 _sig("xg_batch_wait", c_int, c_void_p, POINTER(XgBatchView))
 _sig("xg_batch_release", c_int, c_void_p)
-_sig("xg_build_replica_words", c_int, c_void_p, c_uint32, c_uint32, c_void_p, c_void_p)
+_sig("xg_build_replica_words", c_int, c_void_p, c_uint32, c_uint32, c_void_p, c_void_p, c_void_p)
 _sig("xg_ics22_placement", c_int, c_void_p, c_void_p, c_uint32, c_uint32, c_uint32, c_uint32, c_double, c_uint32, c_uint32,
      c_void_p, c_void_p, c_void_p)
 _sig("xg_sanity_check_ids", c_int, c_void_p, c_size_t, c_uint32, c_void_p, c_void_p, c_void_p)

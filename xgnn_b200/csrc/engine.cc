@@ -634,8 +634,12 @@ void build_feature_store(Engine &e) {
   size_t n_rep = parted ? (size_t)(V * cfg.replicate_percentage) : 0;
   if (n_rep > n_cached) n_rep = n_cached;
   std::sort(ranks.begin(), ranks.begin() + n_rep);  // replicated tier by node id: resolved by rank/select (replica_words)
-  if (parted && n_cached > n_rep)
-    SAM_XG(xg_shuffle_cache_ranks(ranks.data() + n_rep, n_cached - n_rep));  // cuda_cache_manager_host.cc:162-171
+  if (parted && n_cached > n_rep) {
+    if (n_rep && n_cached == V)  // all cached: node-id order (round-robin over parts), covered by the rank/select words
+      std::sort(ranks.begin() + n_rep, ranks.end());
+    else
+      SAM_XG(xg_shuffle_cache_ranks(ranks.data() + n_rep, n_cached - n_rep));  // cuda_cache_manager_host.cc:162-171
+  }
   if (!ics22) {
     std::vector<uint32_t> table(V, XG_EMPTY_KEY);
     for (size_t r = 0; r < n_cached; ++r) table[ranks[r]] = (uint32_t)r;
@@ -716,7 +720,8 @@ void build_feature_store(Engine &e) {
     e.store.replica = gather_rows_to_device(ranks.data(), n_rep);
     e.store.num_replicated = (uint32_t)n_rep;
     void *words = dev_alloc(e, ((V + 31) / 32) * 8);
-    SAM_XG(xg_build_replica_words(e.store.cache_table, (uint32_t)V, (uint32_t)n_rep, words, e.stream));
+    SAM_XG(xg_build_replica_words(e.store.cache_table, (uint32_t)V, (uint32_t)n_rep, words, &e.store.replica_words_cover_all,
+                                  e.stream));
     e.store.replica_words = words;
   }
   const int w = e.worker_id;

@@ -77,7 +77,10 @@ __device__ __forceinline__ uint32_t lookup_rank(const xg_feature_store &st, uint
     // default L2 priority; the rows themselves stream through with evict_first, so the words stay resident
     const uint2 w = __ldg(reinterpret_cast<const uint2 *>(st.replica_words) + (idx >> 5));
     const uint32_t bit = idx & 31u;
-    if ((w.x >> bit) & 1u) return w.y + __popc(w.x & ((1u << bit) - 1u));
+    const uint32_t before = w.y + __popc(w.x & ((1u << bit) - 1u));  // replicated nodes with a smaller id
+    if ((w.x >> bit) & 1u) return before;
+    // every node cached and the sharded tier in node-id order too: its rank is the count of NON-replicated smaller ids
+    if (st.replica_words_cover_all) return st.num_replicated + (idx - before);
   }
   return __ldg(st.cache_table + idx);
 }
@@ -681,13 +684,19 @@ replica_bits_kernel(const uint32_t *__restrict__ table, uint32_t num_node, uint3
 
 __global__ void __launch_bounds__(256)
 replica_words_kernel(const uint32_t *__restrict__ table, uint32_t num_node, const uint32_t *__restrict__ bits,
-                     const uint32_t *__restrict__ prefix, uint2 *words, uint32_t num_words, unsigned long long *mismatch) {
+                     const uint32_t *__restrict__ prefix, uint2 *words, uint32_t num_words, uint32_t num_replicated,
+                     unsigned long long *mismatch) {
   const uint32_t lane = threadIdx.x & 31;
   for (uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; w < num_words; w += (gridDim.x * blockDim.x) >> 5) {
     const uint32_t b = bits[w], p = prefix[w], v = w * 32 + lane;
     if (lane == 0) words[w] = make_uint2(b, p);
     // select must reproduce the table: the replicated tier has to be laid out by node id
-    if (((b >> lane) & 1u) && table[v] != p + __popc(b & ((1u << lane) - 1u))) atomicAdd(mismatch, 1ull);
+    const uint32_t before = p + __popc(b & ((1u << lane) - 1u));
+    if ((b >> lane) & 1u) {
+      if (table[v] != before) atomicAdd(mismatch, 1ull);
+    } else if (v < num_node && table[v] != num_replicated + (v - before)) {
+      atomicAdd(mismatch + 1, 1ull);  // not "all cached, sharded tier by node id": the table stays in use for these
+    }
   }
 }
 
@@ -695,13 +704,13 @@ replica_words_kernel(const uint32_t *__restrict__ table, uint32_t num_node, cons
 }  // namespace xg
 
 extern "C" int xg_build_replica_words(const uint32_t *d_cache_table, uint32_t num_node, uint32_t num_replicated,
-                                      void *d_words, void *stream) {
+                                      void *d_words, uint32_t *h_cover_all, void *stream) {
   XG_REQUIRE(d_cache_table && d_words, "NULL argument");
   if (num_node == 0) return XG_OK;
   cudaStream_t s = as_stream(stream);
   const uint32_t num_words = (num_node + 31) / 32;
   uint32_t *bits = nullptr, *counts = nullptr, *prefix = nullptr;
-  unsigned long long *mismatch = nullptr, h_mismatch = 0;
+  unsigned long long *mismatch = nullptr, h_mismatch[2] = {0, 0};
   void *temp = nullptr;
   size_t temp_bytes = 0;
   XG_CUDA(cudaMalloc(&bits, (size_t)num_words * 3 * sizeof(uint32_t) + sizeof(unsigned long long) * 2));
@@ -710,7 +719,7 @@ extern "C" int xg_build_replica_words(const uint32_t *d_cache_table, uint32_t nu
   mismatch = reinterpret_cast<unsigned long long *>(bits + (size_t)((num_words * 3 + 1) & ~1u));
   cudaError_t e = cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, counts, prefix, (int)num_words, s);
   if (e == cudaSuccess) e = cudaMalloc(&temp, temp_bytes ? temp_bytes : 16);
-  if (e == cudaSuccess) e = cudaMemsetAsync(mismatch, 0, sizeof(unsigned long long), s);
+  if (e == cudaSuccess) e = cudaMemsetAsync(mismatch, 0, 2 * sizeof(unsigned long long), s);
   if (e == cudaSuccess) {
     const unsigned grid = grid_for(((size_t)num_words * 32 + 255) / 256, 8);
     replica_bits_kernel<<<grid, 256, 0, s>>>(d_cache_table, num_node, num_replicated, bits, counts, num_words);
@@ -718,15 +727,16 @@ extern "C" int xg_build_replica_words(const uint32_t *d_cache_table, uint32_t nu
     e = cub::DeviceScan::ExclusiveSum(temp, temp_bytes, counts, prefix, (int)num_words, s);
     if (e == cudaSuccess) {
       replica_words_kernel<<<grid, 256, 0, s>>>(d_cache_table, num_node, bits, prefix, static_cast<uint2 *>(d_words), num_words,
-                                                mismatch);
+                                                num_replicated, mismatch);
       XG_LAUNCHED();
-      e = cudaMemcpyAsync(&h_mismatch, mismatch, sizeof(h_mismatch), cudaMemcpyDeviceToHost, s);
+      e = cudaMemcpyAsync(h_mismatch, mismatch, sizeof(h_mismatch), cudaMemcpyDeviceToHost, s);
       if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     }
   }
   cudaFree(temp);
   cudaFree(bits);
   XG_CUDA(e);
-  XG_REQUIRE(h_mismatch == 0, "the replicated tier is not laid out by node id (cache_table[v] != rank of v among replicated nodes)");
+  XG_REQUIRE(h_mismatch[0] == 0, "the replicated tier is not laid out by node id (cache_table[v] != rank of v among replicated nodes)");
+  if (h_cover_all) *h_cover_all = h_mismatch[1] == 0 ? 1u : 0u;
   return XG_OK;
 }

@@ -136,6 +136,10 @@ def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale
             n_rep = min(n_cached, int(V * replicate_pct)) if (P > 1 or not flat_when_full) else 0
             ranks = cache_rank_nodes(V, n_cached, n_rep)
             ranks[:n_rep].sort()  # the replicated tier is stored by node id: its rows resolve by rank/select (replica_words)
+            if n_rep and replica_words and n_cached == V:
+                # everything cached: the sharded tier by node id as well (round-robin over the parts in id order is as
+                # balanced as the shuffle) - then rank/select covers every node and the DRAM table is never read
+                ranks[n_rep:].sort()
             table = np.full(V, 0xFFFFFFFF, np.uint32)
             table[ranks] = np.arange(n_cached, dtype=np.uint32)
             st.local["cache_table"] = torch.from_numpy(table.view(np.int32)).to(dev)

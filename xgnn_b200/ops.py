@@ -233,6 +233,7 @@ def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_ta
     assert not (compact_bitwidth and st.num_replicated), "the compact (ICS'22) map has no replicated tier of its own"
     st.compact_bitwidth = compact_bitwidth
     st.replica_words = p(replica_words) if (replica_words is not None and st.num_replicated) else None
+    st.replica_words_cover_all = int(bool(st.replica_words) and getattr(replica_words, "cover_all", False))
     st._keep = [host, cache_table, parts, replica, replica_words]  # raw pointers inside: keep the tensors alive
     return st
 
@@ -460,7 +461,9 @@ def build_replica_words(cache_table: torch.Tensor, num_replicated: int) -> torch
     Raises when the replica is not laid out by node id."""
     V = cache_table.numel()
     words = torch.empty(((V + 31) // 32, 2), dtype=torch.int32, device=cache_table.device)
-    check(lib.xg_build_replica_words(_ptr(cache_table), V, num_replicated, _ptr(words), _stream()))
+    cover = ctypes.c_uint32(0)
+    check(lib.xg_build_replica_words(_ptr(cache_table), V, num_replicated, _ptr(words), ctypes.addressof(cover), _stream()))
+    words.cover_all = bool(cover.value)  # every node cached + sharded tier by node id: the table is never read
     return words
 
 
