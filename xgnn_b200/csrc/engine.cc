@@ -975,7 +975,7 @@ struct PendingTask {
   TaskDesc d;
   Engine::Landing *land = nullptr;
   cudaEvent_t copied = nullptr;
-  double t0 = 0;
+  double t0 = 0, t_recv = 0;
   bool prefetched = false;  // begun while the previous Task was still being gathered
 };
 
@@ -1010,18 +1010,28 @@ std::unique_ptr<PendingTask> recv_begin(Engine &e) {
   return p;
 }
 
+// Wait for the Task's peer copy and hand its stage buffer back to the sampler.  RULE (deadlock freedom): a trainer must not
+// block on the queue - wait for a Task that is still to be produced - while one of its Tasks keeps a stage: the sampler
+// that has to produce that Task may be waiting for exactly this stage (it cycles through kStagePerSampler of them, and
+// another trainer can drain the ones in between).  So stages are released before every blocking dequeue.
+void release_stage(Engine &e, PendingTask &p) {
+  if (p.copied == nullptr) return;  // already released
+  const double t_wait = now_s();
+  SAM_CUDA(cudaEventSynchronize(p.copied));
+  SAM_CUDA(cudaEventDestroy(p.copied));
+  p.copied = nullptr;
+  SAM_CHECK(sem_post(&e.queue->stage_free[p.d.sampler][p.d.stage]) == 0);  // the sampler may overwrite its stage buffer now
+  // time this Task kept the trainer waiting (dequeue + copy when nothing overlapped it, ~0 when prefetched)
+  p.t_recv = p.prefetched ? now_s() - t_wait : now_s() - p.t0;
+}
+
 bool recv_finish(Engine &e, std::unique_ptr<PendingTask> p) {
   if (!p) return false;
-  TaskQueueBlock &q = *e.queue;
+  release_stage(e, *p);
   const TaskDesc &d = p->d;
   Engine::Landing *land = p->land;
   const size_t row_bytes = e.ds.feat_row_bytes();
-  const double t_wait = now_s();
-  SAM_CUDA(cudaEventSynchronize(p->copied));
-  SAM_CUDA(cudaEventDestroy(p->copied));
-  SAM_CHECK(sem_post(&q.stage_free[d.sampler][d.stage]) == 0);  // the sampler may overwrite its stage buffer now
-  // time this Task kept the trainer waiting (dequeue + copy when nothing overlapped it, ~0 when prefetched)
-  const double t_recv = p->prefetched ? now_s() - t_wait : now_s() - p->t0;
+  const double t_recv = p->t_recv;
   auto at = [&](uint64_t off) -> const uint32_t * {
     return off == kNone ? nullptr : reinterpret_cast<const uint32_t *>(static_cast<const char *>(land->xfer) + off);
   };
@@ -1381,6 +1391,7 @@ static void extract_loop(Engine *e, long count) {  // DistEngine::StartExtract (
   SAM_CUDA(cudaSetDevice(e->device));
   std::unique_ptr<PendingTask> next;
   for (long i = 0; i < count; ++i) {
+    if (next) release_stage(*e, *next);  // its copy ran under the previous gather: do not sit on the stage while the pool is full
     {
       std::unique_lock<std::mutex> lk(e->mu);
       e->cv.wait(lk, [&] { return e->pool.size() < 2 || e->shutdown; });
@@ -1388,11 +1399,18 @@ static void extract_loop(Engine *e, long count) {  // DistEngine::StartExtract (
     }
     if (!next) next = recv_begin(*e);
     std::unique_ptr<PendingTask> cur = std::move(next);
-    if (i + 1 < count) {  // Task i+1 crosses NVLink while Task i's rows are gathered
+    if (!cur) break;
+    release_stage(*e, *cur);  // before the (possibly blocking) dequeue below: see release_stage
+    if (i + 1 < count) {      // Task i+1 crosses NVLink while Task i's rows are gathered
       next = recv_begin(*e);
       if (next) next->prefetched = true;
     }
     if (!recv_finish(*e, std::move(cur))) break;
+  }
+  if (next) {  // shutdown in mid-flight: give the stage and the landing buffer back
+    release_stage(*e, *next);
+    std::lock_guard<std::mutex> lk(e->mu);
+    next->land->busy = false;
   }
 }
 
