@@ -97,3 +97,16 @@ def _worker(rank, world, port, V, n_train, batch, replicate):
 @pytest.mark.parametrize("world,replicate", [(2, 0.0), (2, 0.3), (3, 0.25)])
 def test_work_and_data_split_tile_the_job(world, replicate):
     mp.spawn(_worker, args=(world, _free_port(), 20011, 1001, 64, replicate), nprocs=world, join=True)
+
+
+def test_arch5_queue_protocol_model_is_deadlock_free():
+    """Thread model of the arch5 Task hand-over (tools/arch5_queue_model.py = the semaphore protocol of engine.cc:
+    stage ring per sampler, ticketed descriptor ring, one synchronous and one prefetching trainer): with the shipped rule
+    - a trainer releases every stage it holds before a blocking dequeue - every Task is delivered exactly once and nothing
+    ever waits forever, across random sampler / consumer speeds (2 samplers x 2 trainers, the configuration in which the
+    first version of the extract loop deadlocked on a B200 box)."""
+    sys.path.insert(0, str(ROOT / "tools"))
+    import arch5_queue_model as M
+    M.TIMEOUT = 3.0
+    for seed in range(40):
+        assert M.run_trial(seed, hold_stage_while_dequeuing=False), f"seed {seed}"
