@@ -110,3 +110,44 @@ def test_arch5_queue_protocol_model_is_deadlock_free():
     M.TIMEOUT = 3.0
     for seed in range(40):
         assert M.run_trial(seed, hold_stage_while_dequeuing=False), f"seed {seed}"
+
+
+def _ics22_worker(rank, world, port, V, n_cached, clique, alpha):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import ctypes
+
+        import oracle_lib as O
+        from xgnn_b200._clib import check, lib
+        rng = np.random.default_rng(99)  # same graph in every process, as the shared dataset is
+        indices = np.minimum((rng.pareto(1.1, V * 10) * 4).astype(np.int64), V - 1).astype(np.uint32)
+        rank_nodes, rank_w = O.ics22_in_degree_rank(indices, V)
+        table, slots, tot = np.empty(V, np.uint32), np.empty(n_cached, np.uint32), ctypes.c_uint32(0)
+        check(lib.xg_ics22_placement(rank_nodes.ctypes.data, rank_w.ctypes.data, V, n_cached, world, clique, alpha, rank, 3,
+                                     table.ctypes.data, slots.ctypes.data, ctypes.addressof(tot)))
+        # what FeatureLoad shares over IPC: every worker's slot list; what each worker keeps private: its map
+        all_slots = _gather_arrays(slots, world)
+        totals = _gather_arrays(np.array([tot.value], np.uint32), world)
+        assert len({int(t[0]) for t in totals}) == 1, "every worker must see the same number of cached nodes"
+        cached = np.nonzero(table != 0xFFFFFFFF)[0]
+        assert len(cached) == tot.value
+        owner, row = table[cached] >> 29, table[cached] & ((1 << 29) - 1)
+        first = rank // clique * clique
+        assert np.all((owner >= first) & (owner < first + clique)), "reads stay inside the clique"
+        for v, o, r in zip(cached, owner, row):
+            assert all_slots[o][r] == v, "my map names a slot that holds another node"
+        # the hottest nodes that were not split away are served from my own HBM
+        assert table[rank_nodes[0]] >> 29 == rank or tot.value > n_cached
+        # distinct nodes held by the clique == total (nothing is cached twice once its slot was split)
+        held = np.unique(np.concatenate(all_slots[first:first + clique]))
+        assert len(held) == tot.value
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,clique,alpha", [(2, 2, 0.0), (2, 1, 0.0), (4, 2, 0.4)])
+def test_ics22_views_of_all_workers_agree(world, clique, alpha):
+    """Each worker derives only ITS view of the ICS'22 clique placement (xg_ics22_placement); together the views must
+    describe one consistent layout: a (owner, row) named by any worker's map holds that node in the owner's slot list."""
+    mp.spawn(_ics22_worker, args=(world, _free_port(), 4001, 300, clique, alpha), nprocs=world, join=True)
