@@ -13,4 +13,4 @@ def test_arch5_decoupled_sampler_and_trainer_processes(dataset, sample_type, sam
     (reference: D2H + 50 MB host ring + H2D, memory_queue.cc / task_queue.cc).  Every Task reaches exactly one trainer
     and carries the oracle's blocks and CPUExtract's rows bit for bit."""
     import torch
-    _drive("arch5", dataset, sample_type, samplers, trainers, env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count()))})
+    _drive("arch5", dataset, sample_type, samplers, trainers, env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "SAMGRAPH_QUEUE_TIMEOUT": "60"})

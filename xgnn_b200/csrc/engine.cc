@@ -872,6 +872,13 @@ bool produce_one(Engine &e) {
 // arch5 task hand-over (see TaskQueueBlock).  Sampler side = MessageTaskQueue::Send (task_queue.cc:332-367), trainer side
 // = MessageTaskQueue::Recv + DoGPUFeatureExtract/DoGPULabelExtract... of RunArch5 extract loops (dist_loops_arch5.cc).
 bool sem_wait_or_shutdown(Engine &e, sem_t *sem) {
+  // SAMGRAPH_QUEUE_TIMEOUT seconds (default 600; covers a trainer still loading its cache) without the other side posting = it is gone (crashed child, lost Task):
+  // fail with a message like any violated CHECK instead of hanging every process of the job
+  static const double limit = [] {
+    const char *s = std::getenv("SAMGRAPH_QUEUE_TIMEOUT");
+    return s ? std::atof(s) : 600.0;
+  }();
+  const double t_begin = now_s();
   for (;;) {
     timespec ts;
     clock_gettime(CLOCK_REALTIME, &ts);
@@ -879,6 +886,7 @@ bool sem_wait_or_shutdown(Engine &e, sem_t *sem) {
     if (ts.tv_nsec >= 1000000000L) { ts.tv_sec += 1; ts.tv_nsec -= 1000000000L; }
     if (sem_timedwait(sem, &ts) == 0) return true;
     SAM_CHECK_MSG(errno == ETIMEDOUT || errno == EINTR, "sem_timedwait failed");
+    SAM_CHECK_MSG(limit <= 0 || now_s() - t_begin < limit, "arch5 task queue: the other side has not posted for SAMGRAPH_QUEUE_TIMEOUT seconds");
     std::lock_guard<std::mutex> lk(e.mu);
     if (e.shutdown) return false;
   }
