@@ -1,0 +1,285 @@
+// TEST INFRASTRUCTURE ONLY -- not part of the product path.
+//
+// Glue that lets the reference's own CUDA samplers be compiled *in place* from /root/reference
+// (oracle/Makefile, target `refcuda`) into oracle/_ref/libxgnn_ref_cuda.so and driven from
+// tests/ as a second oracle for the sampler families whose CPU files are empty stubs
+// (cpu/cpu_sampling_khop1.cc:24-27, cpu_sampling_weighted_khop.cc:24-28,
+// cpu_sampling_random_walk.cc:24-28): KHop1, weighted KHop (alias / prefix / hash-dedup),
+// random walk + FrequencyHashmap::GetTopK, plus the GPU KHop0 / KHop3 kernels.
+//
+// Nothing here restates reference logic.  This file provides
+//   * a cudaMalloc-backed `Device` (the reference's GPUDevice pulls in its workspace pool,
+//     engine and run-config machinery: cuda/cuda_device.cc),
+//   * no-op `Profiler` methods (profiler.cc needs the Engine singleton),
+//   * a flat extern "C" interface: host arrays in, host arrays out.
+//
+// The reference seeds curand from the wall clock (cuda/cuda_random_states.cu:106-108), so its
+// output is not reproducible: tests compare distributions (two-sample chi-square) and the
+// cases where the result does not depend on the draws.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <tuple>
+#include <vector>
+
+#include "common/common.h"
+#include "common/constant.h"
+#include "common/cuda/cuda_frequency_hashmap.h"
+#include "common/cuda/cuda_function.h"
+#include "common/cuda/cuda_random_states.h"
+#include "common/cuda/dist_graph.h"
+#include "common/device.h"
+#include "common/logging.h"
+#include "common/profiler.h"
+#include "common/run_config.h"
+
+#define SHIM_CUDA(x)                                                                      \
+  do {                                                                                    \
+    cudaError_t e_ = (x);                                                                 \
+    if (e_ != cudaSuccess) {                                                              \
+      fprintf(stderr, "ref_cuda_shim %s:%d: %s\n", __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      abort();                                                                            \
+    }                                                                                     \
+  } while (0)
+
+namespace samgraph {
+namespace common {
+
+namespace {
+// GPU contexts: cudaMalloc; CPU contexts (the host-side solvers in ref_host_shim.cc): malloc.
+class ShimDevice : public Device {
+ public:
+  void SetDevice(Context ctx) override {
+    if (ctx.device_type == kGPU) SHIM_CUDA(cudaSetDevice(ctx.device_id));
+  }
+  void *AllocDataSpace(Context ctx, size_t nbytes, size_t) override {
+    void *p = nullptr;
+    if (nbytes == 0) nbytes = 64;
+    if (ctx.device_type == kGPU) {
+      SHIM_CUDA(cudaMalloc(&p, nbytes));
+    } else if (posix_memalign(&p, 64, nbytes) != 0) {
+      abort();
+    }
+    return p;
+  }
+  void FreeDataSpace(Context ctx, void *ptr) override {
+    if (ctx.device_type == kGPU) SHIM_CUDA(cudaFree(ptr));
+    else free(ptr);
+  }
+  size_t WorkspaceActualSize(Context, void *) override { return 0; }
+  void CopyDataFromTo(const void *from, size_t from_offset, void *to, size_t to_offset,
+                      size_t nbytes, Context ctx_from, Context ctx_to, StreamHandle stream) override {
+    char *dst = static_cast<char *>(to) + to_offset;
+    const char *src = static_cast<const char *>(from) + from_offset;
+    if (ctx_from.device_type != kGPU && ctx_to.device_type != kGPU) {
+      memcpy(dst, src, nbytes);
+      return;
+    }
+    SHIM_CUDA(cudaMemcpyAsync(dst, src, nbytes, cudaMemcpyDefault, static_cast<cudaStream_t>(stream)));
+    SHIM_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  }
+  void StreamSync(Context ctx, StreamHandle stream) override {
+    if (ctx.device_type == kGPU) SHIM_CUDA(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  }
+  void SyncDevice(Context ctx) override {
+    if (ctx.device_type == kGPU) SHIM_CUDA(cudaDeviceSynchronize());
+  }
+};
+ShimDevice g_dev;
+}  // namespace
+
+Device *Device::Get(Context) { return &g_dev; }
+void *Device::AllocWorkspace(Context ctx, size_t nbytes, double) {
+  return AllocDataSpace(ctx, nbytes, kTempAllocaAlignment);
+}
+void Device::FreeWorkspace(Context ctx, void *ptr, size_t) { FreeDataSpace(ctx, ptr); }
+StreamHandle Device::CreateStream(Context) { return nullptr; }
+void Device::FreeStream(Context, StreamHandle) {}
+void Device::SyncStreamFromTo(Context, StreamHandle, StreamHandle) {}
+
+Profiler::Profiler() {}
+Profiler &Profiler::Get() {
+  static Profiler p;
+  return p;
+}
+void Profiler::LogStep(uint64_t, LogStepItem, double) {}
+void Profiler::LogStepAdd(uint64_t, LogStepItem, double) {}
+void Profiler::LogEpochAdd(uint64_t, LogEpochItem, double) {}
+void Profiler::LogInit(LogInitItem, double) {}
+void Profiler::LogInitAdd(LogInitItem, double) {}
+void Profiler::ResetStepEpoch() {}
+
+}  // namespace common
+}  // namespace samgraph
+
+using namespace samgraph::common;
+
+namespace {
+
+template <typename T>
+T *to_device(const T *h, size_t n) {
+  T *d = nullptr;
+  SHIM_CUDA(cudaMalloc(&d, (n ? n : 1) * sizeof(T)));
+  if (n) SHIM_CUDA(cudaMemcpy(d, h, n * sizeof(T), cudaMemcpyHostToDevice));
+  return d;
+}
+
+struct RefCudaGraph {
+  int device = 0;
+  uint32_t num_node = 0;
+  size_t num_edge = 0;
+  uint32_t *indptr = nullptr, *indices = nullptr, *alias = nullptr;
+  float *prob = nullptr, *prefix = nullptr;
+  // curand states live as long as the engine in the reference (dist/dist_engine.cc:431-433) and every kernel
+  // stores them back, so batch k continues where batch k-1 stopped: one object per (sampler, fanout, batch size).
+  std::map<std::tuple<int, size_t, size_t>, cuda::GPURandomStates *> states;
+};
+
+}  // namespace
+
+extern "C" {
+
+// Returns 0 when no CUDA device is usable (callers skip).
+int refcu_available() {
+  int n = 0;
+  return cudaGetDeviceCount(&n) == cudaSuccess && n > 0;
+}
+
+void *refcu_graph_create(int device, const uint32_t *indptr, const uint32_t *indices,
+                         uint32_t num_node, size_t num_edge, const float *prob_table,
+                         const uint32_t *alias_table, const float *prob_prefix_table) {
+  SHIM_CUDA(cudaSetDevice(device));
+  auto *g = new RefCudaGraph();
+  g->device = device;
+  g->num_node = num_node;
+  g->num_edge = num_edge;
+  g->indptr = to_device(indptr, static_cast<size_t>(num_node) + 1);
+  g->indices = to_device(indices, num_edge);
+  if (prob_table) g->prob = to_device(prob_table, num_edge);
+  if (alias_table) g->alias = to_device(alias_table, num_edge);
+  if (prob_prefix_table) g->prefix = to_device(prob_prefix_table, num_edge);
+  return g;
+}
+
+void refcu_graph_destroy(void *h) {
+  auto *g = static_cast<RefCudaGraph *>(h);
+  cudaFree(g->indptr);
+  cudaFree(g->indices);
+  cudaFree(g->prob);
+  cudaFree(g->alias);
+  cudaFree(g->prefix);
+  for (auto &kv : g->states) delete kv.second;
+  delete g;
+}
+
+// Forget the curand states: the next call re-seeds from the wall clock like a fresh engine.
+void refcu_reset_states(void *h) {
+  auto *g = static_cast<RefCudaGraph *>(h);
+  for (auto &kv : g->states) delete kv.second;
+  g->states.clear();
+}
+
+// One call of a reference GPU sampler.  sample_type uses the reference numbering (common.h:50-59):
+// 0 KHop0, 1 KHop1, 2 WeightedKHop, 3 RandomWalk, 4 WeightedKHopPrefix, 5 KHop2,
+// 6 WeightedKHopHashDedup, 7 KHop3.  For random walk `fanout` is K (num_neighbor) and
+// out_data receives the visit counts.  out_* are host arrays of capacity num_input * fanout.
+// Returns the number of output edges.
+size_t refcu_sample(void *h, int sample_type, const uint32_t *input, size_t num_input,
+                    size_t fanout, size_t random_walk_length, double restart_prob,
+                    size_t num_random_walk, uint32_t *out_src, uint32_t *out_dst,
+                    uint32_t *out_data) {
+  auto *g = static_cast<RefCudaGraph *>(h);
+  SHIM_CUDA(cudaSetDevice(g->device));
+  Context ctx = GPU(g->device);
+  RunConfig::num_random_walk = num_random_walk;
+  RunConfig::random_walk_length = random_walk_length;
+  RunConfig::random_walk_restart_prob = restart_prob;
+
+  const size_t cap = num_input * fanout;
+  uint32_t *d_input = to_device(input, num_input);
+  uint32_t *d_src = nullptr, *d_dst = nullptr, *d_data = nullptr;
+  size_t *d_num_out = nullptr;
+  SHIM_CUDA(cudaMalloc(&d_src, (cap ? cap : 1) * 4));
+  SHIM_CUDA(cudaMalloc(&d_dst, (cap ? cap : 1) * 4));
+  SHIM_CUDA(cudaMalloc(&d_data, (cap ? cap : 1) * 4));
+  SHIM_CUDA(cudaMalloc(&d_num_out, sizeof(size_t)));
+  SHIM_CUDA(cudaMemset(d_num_out, 0, sizeof(size_t)));
+
+  // GPURandomStates sizes itself from (sample_type, fanout list, batch size): with a one-layer
+  // list {fanout} and batch = num_input it covers exactly the threads one call launches.
+  std::vector<size_t> fan{fanout};
+  auto key = std::make_tuple(sample_type, fanout, num_input);
+  if (!g->states.count(key)) {
+    g->states[key] = new cuda::GPURandomStates(static_cast<SampleType>(sample_type), fan, num_input, ctx);
+    SHIM_CUDA(cudaDeviceSynchronize());
+  }
+  cuda::GPURandomStates &states = *g->states[key];
+  StreamHandle stream = nullptr;
+  cuda::DeviceNormalGraph graph(g->indptr, g->indices, g->num_node);
+
+  switch (sample_type) {
+    case kKHop0:
+      cuda::GPUSampleKHop0(graph, d_input, num_input, fanout, d_src, d_dst, d_num_out, ctx, stream,
+                           &states, 0);
+      break;
+    case kKHop1:
+      cuda::GPUSampleKHop1(g->indptr, g->indices, d_input, num_input, fanout, d_src, d_dst,
+                           d_num_out, ctx, stream, &states, 0);
+      break;
+    case kWeightedKHop:
+      cuda::GPUSampleWeightedKHop(g->indptr, g->indices, g->prob, g->alias, d_input, num_input,
+                                  fanout, d_src, d_dst, d_num_out, ctx, stream, &states, 0);
+      break;
+    case kWeightedKHopPrefix:
+      cuda::GPUSampleWeightedKHopPrefix(g->indptr, g->indices, g->prefix, d_input, num_input,
+                                        fanout, d_src, d_dst, d_num_out, ctx, stream, &states, 0);
+      break;
+    case kKHop2:
+      cuda::GPUSampleKHop2(g->indptr, g->indices, d_input, num_input, fanout, d_src, d_dst,
+                           d_num_out, ctx, stream, &states, 0);
+      break;
+    case kWeightedKHopHashDedup:
+      cuda::GPUSampleWeightedKHopHashDedup(g->indptr, g->indices, g->prob, g->alias, d_input,
+                                           num_input, fanout, d_src, d_dst, d_num_out, ctx, stream,
+                                           &states, 0);
+      break;
+    case kKHop3:
+      cuda::GPUSampleKHop3(graph, d_input, num_input, fanout, d_src, d_dst, d_num_out, ctx, stream,
+                           &states, 0);
+      break;
+    case kRandomWalk: {
+      // dist/dist_engine.cc:436-442
+      cuda::FrequencyHashmap fmap(num_input, num_random_walk * random_walk_length, ctx);
+      cuda::GPUSampleRandomWalk(graph, d_input, num_input, random_walk_length, restart_prob,
+                                num_random_walk, fanout, d_src, d_dst, d_data, d_num_out, &fmap,
+                                ctx, stream, &states, 0);
+      SHIM_CUDA(cudaDeviceSynchronize());
+      break;
+    }
+    default:
+      fprintf(stderr, "refcu_sample: unknown sample type %d\n", sample_type);
+      abort();
+  }
+  SHIM_CUDA(cudaDeviceSynchronize());
+  size_t num_out = 0;
+  SHIM_CUDA(cudaMemcpy(&num_out, d_num_out, sizeof(size_t), cudaMemcpyDeviceToHost));
+  if (num_out > cap) {
+    fprintf(stderr, "refcu_sample: num_out %zu > capacity %zu\n", num_out, cap);
+    abort();
+  }
+  if (out_src) SHIM_CUDA(cudaMemcpy(out_src, d_src, num_out * 4, cudaMemcpyDeviceToHost));
+  if (out_dst) SHIM_CUDA(cudaMemcpy(out_dst, d_dst, num_out * 4, cudaMemcpyDeviceToHost));
+  if (out_data && sample_type == kRandomWalk)
+    SHIM_CUDA(cudaMemcpy(out_data, d_data, num_out * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_input);
+  cudaFree(d_src);
+  cudaFree(d_dst);
+  cudaFree(d_data);
+  cudaFree(d_num_out);
+  return num_out;
+}
+
+}  // extern "C"

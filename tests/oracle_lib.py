@@ -16,6 +16,9 @@ EMPTY = 0xFFFFFFFF
 
 orc = ctypes.CDLL(str(ORACLE_SO))
 ref = ctypes.CDLL(str(REF_SO)) if REF_SO.exists() else None
+# the reference's CUDA samplers + ICS'22 solver + PreSampler compiled in place (oracle/Makefile `refcuda`)
+REF_CUDA_SO = ROOT / "oracle" / "_ref" / "libxgnn_ref_cuda.so"
+refcu = ctypes.CDLL(str(REF_CUDA_SO)) if REF_CUDA_SO.exists() else None
 
 u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
 
@@ -476,3 +479,71 @@ def extract_ics22(parts, table, host_feat, nodes, bitwidth=3):
         t = int(table[v])
         out[i] = host_feat[v] if t == 0xFFFFFFFF else parts[t >> shift][t & ((1 << shift) - 1)]
     return out
+
+
+# ---- the reference's own code compiled in place (oracle/_ref/libxgnn_ref_cuda.so) ---------------------------------
+if refcu is not None:
+    _sig(refcu, "refcu_available", c_int)
+    _sig(refcu, "refcu_graph_create", c_void_p, c_int, u32p, u32p, c_uint32, c_size_t, c_void_p, c_void_p, c_void_p)
+    _sig(refcu, "refcu_graph_destroy", None, c_void_p)
+    _sig(refcu, "refcu_reset_states", None, c_void_p)
+    _sig(refcu, "refcu_sample", c_size_t, c_void_p, c_int, u32p, c_size_t, c_size_t, c_size_t, c_double, c_size_t, u32p,
+         u32p, u32p)
+    _sig(refcu, "ref_ics22_solve", c_uint32, c_void_p, c_uint32, c_uint32, c_uint32, c_double, c_uint32, u32p, u32p, u32p,
+         u32p)
+    _sig(refcu, "ref_presample_rank", None, c_uint32, c_int, c_size_t, u32p, c_void_p, u32p, u32p)
+
+
+def ref_ics22_solve(weight, num_cached, num_dev, clique_size, alpha):
+    """The reference's ICS22SongPlacementSolver itself (cuda/ics22_song_dist_feature.cc:22-167); same return
+    tuple as ics22_placement() above."""
+    w = np.ascontiguousarray(weight, np.float64)
+    V = len(w)
+    ranking = np.empty(V, np.uint32)
+    dev_map, idx_map = np.empty((num_dev, V), np.uint32), np.empty((num_dev, V), np.uint32)
+    cached = np.empty((num_dev, max(num_cached, 1)), np.uint32)
+    total = refcu.ref_ics22_solve(w.ctypes.data, V, num_cached, num_dev, alpha, clique_size, ranking, dev_map.reshape(-1),
+                                  idx_map.reshape(-1), cached.reshape(-1)[:max(num_dev * num_cached, 1)])
+    cached = cached.reshape(-1)[:num_dev * num_cached].reshape(num_dev, num_cached)
+    return ranking, dev_map, idx_map, cached, int(total)
+
+
+def ref_presample_rank(num_node, input_node_lists, epochs=1):
+    """The reference's dist::PreSampler (dist/pre_sampler.cc:40-165) fed with one input-node list per batch."""
+    lists = [u32(a) for a in input_node_lists]
+    assert len(lists) % epochs == 0
+    nodes = np.concatenate(lists + [np.zeros(1, np.uint32)])
+    off = np.cumsum([0] + [len(a) for a in lists]).astype(np.uint64)
+    rank_nodes, rank_freq = np.empty(num_node, np.uint32), np.empty(num_node, np.uint32)
+    refcu.ref_presample_rank(num_node, epochs, len(lists) // epochs, nodes, off.ctypes.data, rank_nodes, rank_freq)
+    return rank_nodes, rank_freq
+
+
+class RefCudaGraph:
+    """A CSR (+ optional weight tables) resident on the GPU for the reference's own CUDA samplers."""
+
+    def __init__(self, indptr, indices, prob=None, alias=None, prefix=None, device=0):
+        self._keep = [u32(indptr), u32(indices),
+                      None if prob is None else np.ascontiguousarray(prob, np.float32),
+                      None if alias is None else u32(alias),
+                      None if prefix is None else np.ascontiguousarray(prefix, np.float32)]
+        k = self._keep
+        self.h = refcu.refcu_graph_create(device, k[0], k[1], len(k[0]) - 1, len(k[1]), _p(k[2]), _p(k[3]), _p(k[4]))
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            refcu.refcu_graph_destroy(self.h)
+            self.h = None
+
+    def reset_states(self):
+        """drop the curand states: the next call seeds fresh ones from the wall clock (cuda_random_states.cu:106-108)"""
+        refcu.refcu_reset_states(self.h)
+
+    def sample(self, sample_type, inp, fanout, walk_length=0, restart_prob=0.0, num_walk=0):
+        """-> (src, dst, data) as the reference's GPUSample* wrote them (data only for random walk)"""
+        inp = u32(inp)
+        cap = max(len(inp) * fanout, 1)
+        src, dst, data = np.empty(cap, np.uint32), np.empty(cap, np.uint32), np.empty(cap, np.uint32)
+        n = refcu.refcu_sample(self.h, sample_type, inp, len(inp), fanout, walk_length, restart_prob, num_walk, src,
+                               dst, data)
+        return src[:n].copy(), dst[:n].copy(), data[:n].copy()

@@ -215,3 +215,6 @@ def test_presample_rank_bit_exact_vs_oracle(ops, small):
     assert np.array_equal(u32(rank_freq), want_freq)
     assert np.array_equal(u32(rank_nodes), want_nodes)
     assert want_freq[0] >= want_freq[-1] and sorted(want_nodes.tolist()) == list(range(small["V"]))
+    if O.refcu is not None:  # the reference's own PreSampler (dist/pre_sampler.cc:40-165, compiled in place) on the same lists
+        ref_nodes, ref_freq = O.ref_presample_rank(small["V"], lists)
+        assert np.array_equal(u32(rank_nodes), ref_nodes) and np.array_equal(u32(rank_freq), ref_freq)

@@ -260,3 +260,92 @@ def test_ics22_placement_rejects_bad_arguments():
     assert lib.xg_ics22_placement(*args(w=4)) != 0   # worker out of range
     assert lib.xg_ics22_placement(*args(b=1)) != 0   # 1 bit cannot name 4 GPUs
     assert lib.xg_ics22_placement(*args(n=9)) != 0   # more slots than nodes
+
+
+# ---- (4) the cache-rank routines pinned against the reference's own code ----------------------------------------------
+# ICS22SongPlacementSolver (cuda/ics22_song_dist_feature.cc:22-167) and dist::PreSampler (dist/pre_sampler.cc:40-165)
+# compiled in place (oracle/ref_host_shim.cc): golden fixtures generated from them (tests/golden/make_golden_rank.py)
+# and, where oracle/_ref/libxgnn_ref_cuda.so is present, the live code.
+RANK_GOLD = np.load(Path(__file__).parent / "golden" / "ref_rank_small.npz")
+needs_refcu = pytest.mark.skipif(O.refcu is None, reason="oracle/_ref/libxgnn_ref_cuda.so not built")
+sys_path_golden = str(Path(__file__).parent / "golden")
+
+
+def _rank_cases():
+    import sys
+    if sys_path_golden not in sys.path:
+        sys.path.insert(0, sys_path_golden)
+    import make_golden_rank as G
+    return G
+
+
+def _product_ics22_views(rank_nodes, rank_w, V, n_cached, num_dev, clique, alpha):
+    import ctypes
+    from xgnn_b200._clib import check, lib
+    views = []
+    for w in range(num_dev):
+        table = np.empty(V, np.uint32)
+        slot_nodes = np.empty(max(n_cached, 1), np.uint32)
+        tot = ctypes.c_uint32(0)
+        check(lib.xg_ics22_placement(rank_nodes.ctypes.data, rank_w.ctypes.data, V, n_cached, num_dev, clique, alpha, w, 3,
+                                     table.ctypes.data, slot_nodes.ctypes.data, ctypes.addressof(tot)))
+        views.append((table, slot_nodes[:n_cached], tot.value))
+    return views
+
+
+@pytest.mark.parametrize("case", range(8))
+def test_ics22_oracle_and_product_match_reference_golden(case):
+    """restatement == reference solver output, and xg_ics22_placement's per-worker view == the compact table built
+    from the REFERENCE's maps (cuda_cache_manager_host.cc:203-222), for every worker"""
+    G = _rank_cases()
+    V, n_cached, num_dev, clique, alpha = G.ICS22_CASES[case]
+    indices, weight = G.ics22_weight(V, num_dev)
+    g = {k: RANK_GOLD[f"ics22_{case}_{k}"] for k in ("ranking", "dev_map", "idx_map", "cached", "total")}
+    ranking, dev_map, idx_map, cached, total = O.ics22_placement(weight, n_cached, num_dev, clique, alpha)
+    assert np.array_equal(ranking, g["ranking"]) and total == int(g["total"])
+    assert np.array_equal(dev_map, g["dev_map"]) and np.array_equal(idx_map, g["idx_map"])
+    assert np.array_equal(cached, g["cached"])
+    rank_nodes, rank_w = O.ics22_in_degree_rank(indices, V)
+    assert np.array_equal(rank_nodes, g["ranking"])
+    for w, (table, slots, tot) in enumerate(_product_ics22_views(rank_nodes, rank_w, V, n_cached, num_dev, clique, alpha)):
+        assert tot == int(g["total"])
+        assert np.array_equal(table, O.ics22_compact_table(g["ranking"], g["dev_map"], g["idx_map"], int(g["total"]), w))
+        assert np.array_equal(slots, g["cached"][w])
+
+
+@needs_refcu
+@pytest.mark.parametrize("V,n_cached,num_dev,clique,alpha", [
+    (257, 33, 4, 2, 0.0), (257, 33, 4, 4, 0.25), (500, 100, 8, 8, 0.0), (500, 499, 8, 2, 0.0), (80, 1, 2, 2, 0.0),
+    (1000, 300, 6, 3, 0.6), (333, 50, 5, 1, 0.0), (90, 0, 2, 2, 0.0)])
+def test_ics22_product_matches_reference_solver_live(V, n_cached, num_dev, clique, alpha):
+    rng = np.random.default_rng(V + n_cached)
+    indices = np.minimum((rng.pareto(1.1, V * 9) * 4).astype(np.int64), V - 1).astype(np.uint32)
+    weight = np.bincount(indices, minlength=V).astype(np.float64)
+    ranking, dev_map, idx_map, cached, total = O.ref_ics22_solve(weight, n_cached, num_dev, clique, alpha)
+    r2 = O.ics22_placement(weight, n_cached, num_dev, clique, alpha)
+    assert all(np.array_equal(a, b) for a, b in zip((ranking, dev_map, idx_map, cached), r2[:4])) and total == r2[4]
+    rank_nodes, rank_w = O.ics22_in_degree_rank(indices, V)
+    assert np.array_equal(rank_nodes, ranking)
+    for w, (table, slots, tot) in enumerate(_product_ics22_views(rank_nodes, rank_w, V, n_cached, num_dev, clique, alpha)):
+        assert tot == total
+        assert np.array_equal(table, O.ics22_compact_table(ranking, dev_map, idx_map, total, w))
+        assert np.array_equal(slots, cached[w])
+
+
+@pytest.mark.parametrize("case,V,n,epochs", [(0, 500, 6, 1), (1, 1000, 8, 2), (2, 64, 3, 3)])
+def test_presample_rank_oracle_matches_reference_golden(case, V, n, epochs):
+    G = _rank_cases()
+    lists = G.presample_lists(V, n * epochs, 77 + case)
+    nodes, freq = O.presample_rank(V, lists)
+    assert np.array_equal(nodes, RANK_GOLD[f"presample_{case}_nodes"])
+    assert np.array_equal(freq, RANK_GOLD[f"presample_{case}_freq"])
+
+
+@needs_refcu
+def test_presample_rank_oracle_matches_reference_live():
+    G = _rank_cases()
+    for seed, (V, n, epochs) in enumerate([(2000, 5, 2), (31, 4, 1), (4096, 12, 1)]):
+        lists = G.presample_lists(V, n * epochs, 1000 + seed)
+        want_nodes, want_freq = O.ref_presample_rank(V, lists, epochs)
+        nodes, freq = O.presample_rank(V, lists)
+        assert np.array_equal(nodes, want_nodes) and np.array_equal(freq, want_freq)

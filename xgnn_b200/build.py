@@ -84,6 +84,8 @@ def build_oracle() -> None:
     subprocess.run(["make", "-s", "-C", str(ROOT / "oracle"), "oracle"], check=True)
     if Path("/root/reference/samgraph").is_dir():
         subprocess.run(["make", "-s", "-C", str(ROOT / "oracle"), "ref"], check=True)
+        # the reference's CUDA samplers / ICS'22 solver / PreSampler compiled in place for sm_100 (second oracle, tests only)
+        subprocess.run(["make", "-s", "-j8", "-C", str(ROOT / "oracle"), "refcuda"], check=True)
 
 
 def build_all(verbose: bool = False, force: bool = False) -> Path:
