@@ -77,6 +77,23 @@ void Device::SyncStreamFromTo(Context, StreamHandle, StreamHandle) {}
 
 using namespace samgraph::common;
 
+// Working buffers live across calls, as in the reference: DoCPUSample / DoFeatureExtract take theirs from the
+// device's workspace pool (cpu/cpu_loops.cc:55-228, workspace_pool.cc), which recycles blocks, so a steady-state
+// batch neither allocates nor zero-fills.  (r01 allocated fresh zero-filled std::vectors inside the timed region:
+// ~2.6 GB of first-touch page faults per batch charged to the reference.)  Grow-only; never shrunk.
+namespace {
+struct Arch0Pool {
+  std::vector<uint32_t> out_src, out_dst, unique, cur, new_src, new_dst;
+  std::vector<char> feat, label;
+};
+Arch0Pool g_pool;
+template <typename T>
+T *at_least(std::vector<T> &v, size_t n) {
+  if (v.size() < n) v.resize(n + n / 8);
+  return v.data();
+}
+}  // namespace
+
 extern "C" {
 
 void ref_set_threads(int n) { RunConfig::omp_thread_num = n; }
@@ -163,6 +180,7 @@ size_t ref_arch0_batch(void *hashtable, int sample_type /*0=khop0, 5=khop2*/,
                        size_t *num_input_nodes, double *sample_seconds, double *extract_seconds) {
   auto *ht = static_cast<cpu::CPUHashTable *>(hashtable);
   auto *out = static_cast<RefBatchOut *>(batch_out);
+  Arch0Pool &pool = g_pool;
   auto t_begin = std::chrono::steady_clock::now();
   ht->Reset();
   ht->Populate(seeds, num_seeds);
@@ -171,53 +189,57 @@ size_t ref_arch0_batch(void *hashtable, int sample_type /*0=khop0, 5=khop2*/,
     out->cols.assign(num_layers, {});
     out->counts.assign(3 * num_layers, 0);
   }
-  std::vector<uint32_t> cur(seeds, seeds + num_seeds);
+  uint32_t *cur = at_least(pool.cur, num_seeds);
+  memcpy(cur, seeds, num_seeds * sizeof(uint32_t));
+  size_t num_cur = num_seeds;
   size_t total = 0;
   for (int i = num_layers - 1; i >= 0; --i) {
     const size_t fanout = fanouts[i];
-    const size_t num_input = cur.size();
-    std::vector<uint32_t> out_src(num_input * fanout), out_dst(num_input * fanout);
+    const size_t num_input = num_cur;
+    uint32_t *out_src = at_least(pool.out_src, num_input * fanout);
+    uint32_t *out_dst = at_least(pool.out_dst, num_input * fanout);
     size_t num_out = 0;
     if (sample_type == 0) {
-      cpu::CPUSampleKHop0(indptr, indices, cur.data(), num_input, out_src.data(), out_dst.data(),
-                          &num_out, fanout);
+      cpu::CPUSampleKHop0(indptr, indices, cur, num_input, out_src, out_dst, &num_out, fanout);
     } else {
-      cpu::CPUSampleKHop2(indptr, indices, cur.data(), num_input, out_src.data(), out_dst.data(),
-                          &num_out, fanout);
+      cpu::CPUSampleKHop2(indptr, indices, cur, num_input, out_src, out_dst, &num_out, fanout);
     }
-    ht->Populate(out_dst.data(), num_out);
+    ht->Populate(out_dst, num_out);
     size_t num_unique = ht->NumItems();
-    std::vector<uint32_t> unique(num_unique);
-    ht->MapNodes(unique.data(), num_unique);
-    std::vector<uint32_t> new_src(num_out), new_dst(num_out);
-    ht->MapEdges(out_src.data(), out_dst.data(), num_out, new_src.data(), new_dst.data());
-    if (out) {
-      out->rows[i] = std::move(new_dst);
-      out->cols[i] = std::move(new_src);
+    uint32_t *unique = at_least(pool.unique, num_unique);
+    ht->MapNodes(unique, num_unique);
+    uint32_t *new_src = at_least(pool.new_src, num_out);
+    uint32_t *new_dst = at_least(pool.new_dst, num_out);
+    ht->MapEdges(out_src, out_dst, num_out, new_src, new_dst);
+    if (out) {  // parity tests only: copy the layer out of the pool
+      out->rows[i].assign(new_dst, new_dst + num_out);
+      out->cols[i].assign(new_src, new_src + num_out);
       out->counts[3 * i + 0] = num_unique;
       out->counts[3 * i + 1] = num_input;
       out->counts[3 * i + 2] = num_out;
     }
-    cur.swap(unique);
+    pool.cur.swap(pool.unique);  // the unique list is the next layer's input
+    cur = pool.cur.data();
+    num_cur = num_unique;
     total += num_out;
   }
   auto t_sampled = std::chrono::steady_clock::now();
-  if (num_input_nodes) *num_input_nodes = cur.size();
+  if (num_input_nodes) *num_input_nodes = num_cur;
+  char *f = nullptr, *l = nullptr;
   if (feat) {
-    std::vector<char> local_feat;
-    std::vector<char> &f = out ? out->feat : local_feat;
-    f.resize(cur.size() * feat_dim * feat_elem_bytes);
-    cpu::CPUExtract(f.data(), feat, cur.data(), cur.size(), feat_dim,
-                    static_cast<DataType>(feat_dtype));
+    f = at_least(pool.feat, num_cur * feat_dim * feat_elem_bytes);
+    cpu::CPUExtract(f, feat, cur, num_cur, feat_dim, static_cast<DataType>(feat_dtype));
   }
   if (label) {
-    std::vector<char> local_label;
-    std::vector<char> &l = out ? out->label : local_label;
-    l.resize(num_seeds * 8);
-    cpu::CPUExtract(l.data(), label, seeds, num_seeds, 1, kI64);
+    l = at_least(pool.label, num_seeds * 8);
+    cpu::CPUExtract(l, label, seeds, num_seeds, 1, kI64);
   }
   auto t_end = std::chrono::steady_clock::now();
-  if (out) out->input_nodes = cur;
+  if (out) {
+    out->input_nodes.assign(cur, cur + num_cur);
+    if (f) out->feat.assign(f, f + num_cur * feat_dim * feat_elem_bytes);
+    if (l) out->label.assign(l, l + num_seeds * 8);
+  }
   if (sample_seconds) *sample_seconds = std::chrono::duration<double>(t_sampled - t_begin).count();
   if (extract_seconds) *extract_seconds = std::chrono::duration<double>(t_end - t_sampled).count();
   return total;

@@ -437,12 +437,16 @@ struct BatchHolder {
   xg_batch_view view{};
   uint64_t key = 0;
   std::function<void()> on_release;  // arch5 trainer: the landing buffers behind `view` go back to their pool
-  ~BatchHolder() {
-    if (batch) xg_batch_release(batch);
-    if (on_release) on_release();
-  }
+  ~BatchHolder();
 };
 using BatchPtr = std::shared_ptr<BatchHolder>;
+
+// a Task that has been handed to the sampler engine but not waited for yet
+struct PendingBatch {
+  BatchPtr holder;
+  size_t epoch = 0;
+  double t_submit = 0, t_shuffle = 0;
+};
 
 struct Engine {
   Dataset ds;
@@ -467,6 +471,14 @@ struct Engine {
   BatchPtr current;
   std::vector<std::thread> threads;
   bool producer_done = false;
+  // Tasks in flight inside the sampler engine (submitted, not yet waited for): the producers keep kInFlight of them
+  // there so that the extract phase of Task k runs beside the sample phase of Task k+1 (pipeline.cu)
+  std::deque<PendingBatch> inflight;
+  bool shuffler_done = false;
+  double last_finish = 0;
+  std::mutex slot_mu;
+  std::condition_variable slot_cv;  // a batch slot went back to the sampler engine
+  uint64_t slot_gen = 0;            // bumped (under slot_mu) by every release: no wake-up can be lost
   // arch5
   TaskQueueBlock *queue = nullptr;
   int role = 0;  // 0 = sampler + trainer in one process (arch0-4, 6), 1 = arch5 sampler, 2 = arch5 trainer
@@ -484,6 +496,18 @@ struct Engine {
   size_t sanity_epoch = (size_t)-1;
 };
 Engine *g_engine = nullptr;
+
+BatchHolder::~BatchHolder() {
+  if (batch) xg_batch_release(batch);
+  if (on_release) on_release();
+  if (batch && g_engine) {
+    {
+      std::lock_guard<std::mutex> lk(g_engine->slot_mu);
+      ++g_engine->slot_gen;
+    }
+    g_engine->slot_cv.notify_all();
+  }
+}
 
 Engine &engine() {
   SAM_CHECK_MSG(g_engine != nullptr, "engine is not created: call samgraph_init or samgraph_data_init first");
@@ -816,29 +840,63 @@ void sanity_check_batch(Engine &e, const xg_batch_view &v, size_t epoch) {
   SAM_CHECK_MSG(bad == 0, "SAMGRAPH_SANITY_CHECK: " + std::to_string(bad) + " violation(s) in batch " + std::to_string(v.key));
 }
 
-void send_task(Engine &e, const xg_batch_view &v, size_t epoch, double sample_time);
+constexpr size_t kInFlight = 2;  // Tasks kept inside the sampler engine: one being sampled + the extract phase of the one before
 
-bool produce_one(Engine &e) {
+// DoShuffle + enqueue: takes the next batch of seeds and hands it to the sampler engine WITHOUT waiting for it.
+// Returns false once every epoch has been handed out.
+bool submit_one(Engine &e) {
   SAM_CHECK_MSG(e.sampler_ready, "sample_init / init has not run");
   create_sampler(e);
-  const double t0 = now_s();
+  if (e.shuffler_done) return false;
+  PendingBatch p;
+  p.t_submit = now_s();
   const uint32_t *d_seeds = nullptr;
-  size_t n = 0, epoch = 0, local_step = 0;
-  if (!e.shuffler->get_batch(e.stream, &d_seeds, &n, &epoch, &local_step)) return false;
-  const double t_shuffle = now_s() - t0;
-  // Engine::GetBatchKey(epoch, step) with the blocked global step (dist_shuffler_aligned.h:38-40, engine.h:50-54)
-  const uint64_t key = epoch * e.num_step + e.shuffler->global_step_offset + local_step;
-  auto holder = std::make_shared<BatchHolder>();
-  holder->key = key;
-  // every slot may still be referenced by tensors the caller holds (from_blob semantics): wait for one to die
-  for (int spins = 0;; ++spins) {
-    const int rc = xg_sampler_submit(e.sampler, d_seeds, n, 1, key, &holder->batch);
-    if (rc == XG_OK) break;
-    SAM_CHECK_MSG(rc == XG_ERR_CAPACITY && spins < 300000, std::string("xg_sampler_submit: ") + xg_last_error());
-    std::this_thread::sleep_for(std::chrono::microseconds(100));
+  size_t n = 0, local_step = 0;
+  if (!e.shuffler->get_batch(e.stream, &d_seeds, &n, &p.epoch, &local_step)) {
+    e.shuffler_done = true;
+    return false;
   }
+  p.t_shuffle = now_s() - p.t_submit;
+  // Engine::GetBatchKey(epoch, step) with the blocked global step (dist_shuffler_aligned.h:38-40, engine.h:50-54)
+  const uint64_t key = p.epoch * e.num_step + e.shuffler->global_step_offset + local_step;
+  p.holder = std::make_shared<BatchHolder>();
+  p.holder->key = key;
+  // every slot may still be referenced by tensors the caller holds (from_blob semantics): block until one dies
+  // (BatchHolder's destructor signals slot_cv); 60 s without any release means the caller leaks batches
+  const double t_wait0 = now_s();
+  for (;;) {
+    uint64_t seen;
+    {
+      std::lock_guard<std::mutex> lk(e.slot_mu);
+      seen = e.slot_gen;
+    }
+    const int rc = xg_sampler_submit(e.sampler, d_seeds, n, 1, key, &p.holder->batch);
+    if (rc == XG_OK) break;
+    SAM_CHECK_MSG(rc == XG_ERR_CAPACITY, std::string("xg_sampler_submit: ") + xg_last_error());
+    SAM_CHECK_MSG(now_s() - t_wait0 < 60.0, "every batch slot is still referenced by caller tensors after 60 s: " +
+                                                std::string(xg_last_error()));
+    std::unique_lock<std::mutex> lk(e.slot_mu);
+    e.slot_cv.wait_for(lk, std::chrono::milliseconds(200), [&] { return e.slot_gen != seen; });
+  }
+  e.inflight.push_back(std::move(p));
+  return true;
+}
+
+void send_task(Engine &e, const xg_batch_view &v, size_t epoch, double sample_time);
+
+// Waits for the OLDEST Task in flight, logs it and hands it on (GraphPool::Submit, or the arch5 queue).
+void finish_one(Engine &e) {
+  SAM_CHECK(!e.inflight.empty());
+  PendingBatch p = std::move(e.inflight.front());
+  e.inflight.pop_front();
+  BatchPtr holder = std::move(p.holder);
   SAM_XG(xg_batch_wait(holder->batch, &holder->view));
-  const double t_total = now_s() - t0;
+  const double t_done = now_s();
+  // with Tasks overlapping inside the engine, a Task's share of the epoch is the time since the previous one finished
+  const double t_total = t_done - std::max(p.t_submit, e.last_finish);
+  e.last_finish = t_done;
+  const uint64_t key = holder->key;
+  const size_t epoch = p.epoch;
   if (e.sanity_check) sanity_check_batch(e, holder->view, epoch);
   double edges = 0;
   for (uint32_t l = 0; l < holder->view.num_layer; ++l) edges += (double)holder->view.num_edge[l];
@@ -847,8 +905,8 @@ bool produce_one(Engine &e) {
   g_prof.log_step(key, kLogL1NumNode, (double)holder->view.num_input, false);
   g_prof.log_step(key, kLogL1SampleTime, t_total, false);  // sample and extract are one fused chain: all of it
   g_prof.log_step(key, kLogL1SampleTotalTime, t_total, false);
-  g_prof.log_step(key, kLogL2ShuffleTime, t_shuffle, false);
-  g_prof.log_step(key, kLogL2CoreSampleTime, t_total - t_shuffle, false);
+  g_prof.log_step(key, kLogL2ShuffleTime, p.t_shuffle, false);
+  g_prof.log_step(key, kLogL2CoreSampleTime, std::max(0.0, t_total - p.t_shuffle), false);
   g_prof.log_step(key, kLogL1CopyTime, 0.0, false);
   g_prof.log_step(key, kLogL1FeatureBytes, feat_bytes, false);
   g_prof.log_step(key, kLogL1LabelBytes, (double)holder->view.num_output * 8, false);
@@ -858,13 +916,26 @@ bool produce_one(Engine &e) {
   g_prof.log_epoch_add(epoch, kLogEpochFeatureBytes, feat_bytes);
   if (e.role == 1) {  // arch5 sampler: the Task goes to a trainer process (RunArch5LoopsOnce / DoGPUSample + Send)
     send_task(e, holder->view, epoch, t_total);
-    return true;       // holder dies here: the slot is free again, the payload lives in the stage buffer
+    return;            // holder dies here: the slot is free again, the payload lives in the stage buffer
   }
   {
     std::lock_guard<std::mutex> lk(e.mu);
     e.pool.push_back(holder);  // GraphPool::Submit
   }
   e.cv.notify_all();
+}
+
+// RunSampleSubLoopOnce + RunCacheDataCopySubLoopOnce for one Task (dist_loops_arch6.cc:55-199): one more Task reaches
+// the pool.  The sampler engine is kept kInFlight Tasks deep, as the reference's background SampleCopySubLoop threads
+// keep its stages busy (dist_loops_arch6.cc:221-243, graph_pool.cc:31-49): Task k+1 is enqueued BEFORE Task k is
+// waited for, so its sample phase overlaps Task k's gather - and, for sample_once callers, the caller's training step.
+// Batch keys, order and contents do not depend on this (the RNG is keyed by the batch key).
+// Returns false once every epoch has been produced.
+bool produce_one(Engine &e) {
+  while (e.inflight.size() < kInFlight && submit_one(e)) {
+  }
+  if (e.inflight.empty()) return false;
+  finish_one(e);
   return true;
 }
 
@@ -1504,6 +1575,7 @@ void samgraph_shutdown(void) {  // operation.cc:397-403
   e.cv.notify_all();
   for (auto &t : e.threads) t.join();
   e.threads.clear();
+  e.inflight.clear();  // Tasks still inside the sampler engine: their slots go back (xg_batch_release waits for them)
   e.pool.clear();
   e.current.reset();
   if (e.stream) cudaStreamSynchronize(e.stream);

@@ -27,8 +27,10 @@ namespace xg {
 
 namespace {
 
+// plain variant: 8 CTAs/SM (32 registers) - the big layer is bound by random-access throughput and every resident
+// warp counts; pipelined variant: registers for 4 nodes in flight instead
 template <int G, int VPL, bool FUSED, bool PIPE>
-__global__ void __launch_bounds__(kSampleBlock)
+__global__ void __launch_bounds__(kSampleBlock, VPL > 1 ? 1 : (PIPE ? 5 : 8))
 sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint32_t num_input_max,
                       const uint32_t *__restrict__ d_num_input, uint32_t fanout,
                       uint32_t *__restrict__ out_src, uint32_t *__restrict__ out_dst,
@@ -113,7 +115,8 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
       constexpr int kPipe = 4;
       static_assert((kSampleTile / kGroups) % kPipe == 0, "tile iterations must be a multiple of the pipeline depth");
       for (unsigned j0 = grp; j0 < kSampleTile; j0 += kGroups * kPipe) {
-        uint32_t nb[kPipe], slot[kPipe], key0[kPipe];
+        uint32_t nb[kPipe], slot[kPipe];
+        unsigned long long old0[kPipe];
         bool live[kPipe];
 #pragma unroll
         for (int q = 0; q < kPipe; ++q) {  // sweep 1: choose the position, issue the neighbour load
@@ -146,7 +149,7 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
           const uint64_t e = tile_base + s_off[j] + gl;
           out_dst[e] = nb[q];
           out_src[e] = s_src[j];
-          if (FUSED) slot[q] = table_insert_begin(fusion.table, nb[q], &key0[q]);
+          if (FUSED) slot[q] = table_insert_begin(fusion.table, nb[q], kPosTag | (uint32_t)e, &old0[q]);
         }
         if (FUSED) {
 #pragma unroll
@@ -154,7 +157,7 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
             if (!live[q]) continue;
             const unsigned j = j0 + q * kGroups;
             const uint64_t e = tile_base + s_off[j] + gl;
-            fusion.pos_out[e] = table_insert_finish(fusion.table, nb[q], kPosTag | (uint32_t)e, slot[q], key0[q]);
+            fusion.pos_out[e] = table_insert_finish(fusion.table, nb[q], kPosTag | (uint32_t)e, slot[q], old0[q]);
           }
         }
       }
