@@ -102,7 +102,9 @@ typedef struct xg_feature_store {
   uint32_t replica_words_cover_all; /* 1 (as reported by xg_build_replica_words): every node is cached and the sharded tier is
                                      * in node-id order as well, cache_table[v] = num_replicated + number of NON-replicated
                                      * nodes with a smaller id - then no lookup reads the table at all */
-  uint32_t reserved;
+  uint32_t host_row_mask; /* 0: `host` has one row per node.  2^k - 1: SAMGRAPH_EMPTY_FEAT=k mock features - `host` has 2^k
+                           * rows and a host-resident node v reads row v & mask (gpu_mock_extract, cuda/cuda_extraction.cu:
+                           * 51-72; extract_miss_data's mask, cuda_cache_manager_device.cu:589-592) */
 } xg_feature_store;
 
 /* ------------------------------------------------------------------------------------------------
@@ -155,7 +157,12 @@ int xg_map_edges(xg_hashtable *t, const uint32_t *d_src, uint32_t *d_new_src, co
  * without replacement; all neighbours in CSR order when degree <= fanout.  The three reference
  * variants differ only in how the deg > fanout subset is drawn; one kernel implements that law here
  * (position sampling, reads exactly min(deg, fanout) neighbours). `sample_type` is accepted for all
- * three (XG_KHOP0 / XG_KHOP2 / XG_KHOP3). */
+ * three (XG_KHOP0 / XG_KHOP2 / XG_KHOP3).
+ * CONCURRENCY of the standalone operators xg_sample_khop, xg_sample_khop1, xg_sample_weighted_khop,
+ * xg_sample_random_walk and xg_get_miss_cache_index: each keeps ONE look-back scan workspace per device, so calls
+ * on the same device must be issued on ONE stream (or be otherwise ordered); the reference's operators have the same
+ * shape of restriction (one workspace pool per device, one sampler stream).  The minibatch engine (xg_sampler_*) and
+ * xg_hashtable_* carry their own per-object workspaces and have no such limit. */
 int xg_sample_khop(const xg_graph *g, int sample_type, const uint32_t *d_input, size_t num_input,
                    size_t fanout, uint32_t *d_out_src, uint32_t *d_out_dst, size_t *d_num_out,
                    uint64_t seed, uint64_t batch_key, void *stream);
@@ -208,6 +215,10 @@ int xg_get_miss_cache_index(const uint32_t *d_cache_table, const uint32_t *d_nod
                             uint32_t *d_miss_src, uint32_t *d_miss_dst, size_t *h_num_miss,
                             uint32_t *d_cache_src, uint32_t *d_cache_dst, size_t *h_num_cache,
                             void *stream);
+/* GPUMockExtract (cuda/cuda_extraction.cu:118-160; CPU twin cpu/cpu_extraction.cc:47-64): dst[i] = src[index[i] & (2^k - 1)],
+ * the SAMGRAPH_EMPTY_FEAT=k mock-feature mode of the reference's evaluation scripts; k = 0 is plain GPUExtract */
+int xg_mock_extract(void *d_dst, const void *src, const uint32_t *d_index, size_t num_index, size_t row_bytes,
+                    unsigned empty_feat_bits, void *stream);
 /* GPUExtractMissData (cuda_cache_manager_device.cu:573-625): out[dst[i]] = host_feat[src[i]] */
 int xg_extract_miss_data(void *d_out, const void *host_feat, const uint32_t *d_miss_src,
                          const uint32_t *d_miss_dst, size_t num_miss, size_t row_bytes, void *stream);

@@ -118,6 +118,13 @@ void ref_cpu_extract(void *dst, const void *src, const uint32_t *index, size_t n
                      size_t dim, int dtype) {
   cpu::CPUExtract(dst, src, index, num_index, dim, static_cast<DataType>(dtype));
 }
+// cpu_extraction.cc:47-64 + 92-118: the SAMGRAPH_EMPTY_FEAT mock variant (row index masked to 2^bits rows)
+void ref_cpu_mock_extract(void *dst, const void *src, const uint32_t *index, size_t num_index,
+                          size_t dim, int dtype, unsigned bits) {
+  RunConfig::option_empty_feat = bits;
+  cpu::CPUMockExtract(dst, src, index, num_index, dim, static_cast<DataType>(dtype));
+  RunConfig::option_empty_feat = 0;
+}
 int ref_dtype_f32() { return kF32; }
 int ref_dtype_f16() { return kF16; }
 int ref_dtype_i64() { return kI64; }

@@ -152,6 +152,16 @@ def extract(src: np.ndarray, index) -> np.ndarray:
     return out
 
 
+def mock_extract(src: np.ndarray, index, empty_feat_bits: int) -> np.ndarray:
+    """CPUMockExtract (cpu/cpu_extraction.cc:47-64): out[i] = src[index[i] & (2^bits - 1)]"""
+    index = u32(index)
+    src = np.ascontiguousarray(src)
+    out = np.empty((len(index),) + src.shape[1:], src.dtype)
+    row_bytes = src.strides[0]
+    orc.orc_mock_extract(out.ctypes.data, src.ctypes.data, index, len(index), row_bytes, empty_feat_bits)
+    return out
+
+
 def route_node(v, num_part, num_cache_node):
     p, r = c_uint32(), c_uint32()
     orc.orc_route_node(v, num_part, num_cache_node, ctypes.byref(p), ctypes.byref(r))
@@ -330,6 +340,18 @@ if ref is not None:
         n = c_size_t()
         ref.ref_cpu_sample_khop0(u32(indptr), u32(indices), inp, len(inp), src, dst, ctypes.byref(n), fanout)
         return src[: n.value].copy(), dst[: n.value].copy()
+
+    def ref_mock_extract(src: np.ndarray, index, bits: int):
+        index = u32(index)
+        src = np.ascontiguousarray(src)
+        dim = src.shape[1] if src.ndim == 2 else 1
+        out = np.empty((len(index),) + src.shape[1:], src.dtype)
+        code = {np.dtype(np.float32): ref.ref_dtype_f32(), np.dtype(np.float16): ref.ref_dtype_f16(),
+                np.dtype(np.int64): ref.ref_dtype_i64(), np.dtype(np.uint8): ref.ref_dtype_u8()}[src.dtype]
+        ref.ref_cpu_mock_extract(ctypes.c_void_p(out.ctypes.data), ctypes.c_void_p(src.ctypes.data),
+                                 index.ctypes.data_as(ctypes.c_void_p), ctypes.c_size_t(len(index)), ctypes.c_size_t(dim),
+                                 code, bits)
+        return out
 
     def ref_extract(src: np.ndarray, index):
         index = u32(index)

@@ -31,6 +31,12 @@ def load(d):
              feat=np.fromfile(os.path.join(d, "feat.bin"), np.float32).reshape(V, dim),
              label=np.fromfile(os.path.join(d, "label.bin"), np.uint64).astype(np.int64),
              train=np.fromfile(os.path.join(d, "train_set.bin"), np.uint32), prob=None, alias=None, prefix=None)
+    k = int(os.environ.get("SAMGRAPH_EMPTY_FEAT", "0"))
+    if k:  # mock features: node v reads row v & (2^k - 1) of the engine's pattern table (engine.cc load_dataset)
+        rb = dim * 4
+        r = np.arange(1 << k, dtype=np.int64)[:, None]
+        table = ((31 * r + np.arange(rb, dtype=np.int64)[None, :]) & 0x3F).astype(np.uint8).view(np.float32)
+        g["feat"] = table[np.arange(V) & ((1 << k) - 1)]
     if os.path.exists(os.path.join(d, "prob_table.bin")):
         g["prob"] = np.fromfile(os.path.join(d, "prob_table.bin"), np.float32)
         g["alias"] = np.fromfile(os.path.join(d, "alias_table.bin"), np.uint32)

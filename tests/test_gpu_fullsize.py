@@ -34,57 +34,8 @@ def _u32(t):  # int32 view -> int64 values of the uint32 bits
 
 
 def check_minibatch_properties(mb, st, D, seeds_np, fanout, uniform=True):
-    dev = mb.input_nodes.device
-    L = mb.num_layer
-    inp = _u32(mb.input_nodes)
-    seeds = torch.from_numpy(seeds_np.astype(np.int64)).to(dev)
-    # ---- unique / remap ----
-    assert inp.numel() == mb.num_input
-    assert torch.unique(inp).numel() == inp.numel(), "input_nodes must be duplicate-free"
-    assert torch.equal(inp[: len(seeds_np)], seeds), "seeds are the prefix of input_nodes, in order"
-    assert int(inp.max()) < st.num_node
-    assert mb.num_dst[L - 1] == len(seeds_np) and mb.num_src[0] == mb.num_input
-    for l in range(L - 1):
-        assert mb.num_dst[l] == mb.num_src[l + 1]  # layer l expands exactly the nodes layer l+1 discovered
-    indptr = _u32(st.local["indptr"])
-    for l in range(L):
-        row, col = _u32(mb.row(l)), _u32(mb.col(l))
-        assert row.numel() == mb.num_edge[l] == col.numel()
-        if row.numel() == 0:
-            continue
-        assert int(row.max()) < mb.num_src[l] and int(col.max()) < mb.num_dst[l]
-        if uniform:
-            # node-major, input order; count == min(deg, fanout) for every expanded node
-            assert bool((col[1:] >= col[:-1]).all())
-            nodes = inp[: mb.num_dst[l]]
-            deg = indptr[nodes + 1] - indptr[nodes]
-            want = torch.clamp(deg, max=fanout[l])
-            got = torch.bincount(col, minlength=mb.num_dst[l])
-            assert torch.equal(got, want)
-            ip = _u32(mb.csc_indptr(l))  # CSC offsets == exclusive scan of the per-node counts
-            assert int(ip[0]) == 0 and torch.equal(ip[1:] - ip[:-1], want)
-            # nodes with degree <= fanout keep their whole list in CSR order (the bit-exact branch): EVERY such edge's
-            # remapped neighbour must be the CSR entry at the same offset - checks sampler + unique + remap at scale
-            whole = deg[col] <= fanout[l]
-            off = torch.arange(col.numel(), device=dev) - ip[col]
-            src_global = nodes[col[whole]]
-            want_dst = _u32(st.local["indices"][indptr[src_global] + off[whole]])
-            assert torch.equal(inp[row[whole]], want_dst), "remapped neighbour differs from the CSR entry"
-        # membership of a sample of edges in the CSR list of their source node
-        g = torch.Generator(device="cpu").manual_seed(l)
-        pick = torch.randint(0, row.numel(), (400,), generator=g).to(dev)
-        src_nodes, dst_nodes = inp[col[pick]], inp[row[pick]]
-        b, e = indptr[src_nodes].cpu().tolist(), indptr[src_nodes + 1].cpu().tolist()
-        dn = dst_nodes.cpu().tolist()
-        for k in range(len(dn)):
-            nbrs = _u32(st.local["indices"][b[k]:e[k]])
-            assert bool((nbrs == dn[k]).any()), "sampled edge is not in the graph"
-    # ---- features / labels: closed form of the generator ----
-    want = D.gen_features(mb.num_input, st.dim, st.dtype, dev, row_ids=mb.input_nodes)
-    got = mb.feat
-    view = torch.int32 if st.dtype == torch.float32 else torch.int16
-    assert torch.equal(got.view(view), want.view(view)), "feature rows differ from the generator (0 ULP bar)"
-    assert torch.equal(mb.label, seeds % st.num_class)
+    from xgnn_b200.selfcheck import check_minibatch_properties as check  # shared with bench.py's per-rank self-check
+    check(mb, st, D, seeds_np, fanout, uniform=uniform)
 
 
 def _run(shape, scale, batches=3, cache_pct=1.0, host_rows=False, need_gb=0.0, flat=True, **sampler_kw):

@@ -467,3 +467,21 @@ def test_extract_two_tier_rank_select_words(P, pct, rep):
     if nrep > 1 and not np.array_equal(policy_table, table):
         bad = torch.empty_like(words)
         assert lib.xg_build_replica_words(dev(policy_table).data_ptr(), V, nrep, bad.data_ptr(), None, None) != 0
+
+
+@gpu
+@pytest.mark.parametrize("dtype,dim,bits", [(np.float32, 128, 8), (np.float16, 768, 4), (np.float32, 100, 1), (np.uint8, 16, 12)])
+def test_mock_extract_matches_oracle(dtype, dim, bits):
+    """GPUMockExtract (cuda/cuda_extraction.cu:51-72,118-160) == CPUMockExtract restatement, byte for byte; and through
+    the GGMS store: host-resident rows are masked, cached rows are whatever the cache was built with"""
+    import torch
+    rng = np.random.default_rng(dim + bits)
+    table = rng.integers(0, 100, size=(1 << bits, dim)).astype(dtype)
+    idx = rng.integers(0, 1 << 22, size=5000).astype(np.uint32)
+    d_table = torch.from_numpy(table).cuda()
+    got = ops.GPUMockExtract(d_table, dev(idx), bits)
+    assert got.cpu().numpy().tobytes() == O.mock_extract(table, idx, bits).tobytes()
+    # a store whose host tier is the mock table: nothing cached -> every row is a masked host row
+    store = ops.make_feature_store(table.strides[0], d_table, None, empty_feat=bits)
+    out = ops.ExtractGGMS(store, dev(idx), dim, d_table.dtype)
+    assert out.cpu().numpy().tobytes() == table[idx & ((1 << bits) - 1)].tobytes()

@@ -349,3 +349,16 @@ def test_presample_rank_oracle_matches_reference_live():
         want_nodes, want_freq = O.ref_presample_rank(V, lists, epochs)
         nodes, freq = O.presample_rank(V, lists)
         assert np.array_equal(nodes, want_nodes) and np.array_equal(freq, want_freq)
+
+
+@needs_ref
+@pytest.mark.parametrize("dtype,dim,bits", [(np.float32, 100, 6), (np.float16, 768, 3), (np.uint8, 7, 10), (np.int64, 1, 1)])
+def test_mock_extract_oracle_matches_reference(dtype, dim, bits):
+    """SAMGRAPH_EMPTY_FEAT: CPUMockExtract (cpu/cpu_extraction.cc:47-64, 92-118) masks the ROW INDEX to 2^bits rows"""
+    rng = np.random.default_rng(bits)
+    table = rng.integers(0, 100, size=(1 << bits, dim)).astype(dtype)
+    idx = rng.integers(0, 1 << 20, size=777).astype(np.uint32)
+    want = O.ref_mock_extract(table, idx, bits)
+    got = O.mock_extract(table, idx, bits)
+    assert got.tobytes() == want.tobytes()
+    assert got.tobytes() == table[idx & ((1 << bits) - 1)].tobytes()

@@ -150,3 +150,14 @@ def test_arch6_ics22_clique_placement(dataset, workers, clique, alpha):
     import torch
     _drive("arch6", dataset, 0, workers,
            env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "XG_TEST_ICS22": f"{clique},{alpha}"})
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode,args,bits", [("single", (0,), 7), ("arch6", (0, 2), 5), ("single", (7,), 12)])
+def test_empty_feat_mock_features(dataset, mode, args, bits):
+    """SAMGRAPH_EMPTY_FEAT=k (run_config.cc:138, engine.cc:198-213): the feature table has 2^k rows and every read -
+    cache build (CPUMockExtract), cache miss (extract_miss_data's mask), flat extract (GPUMockExtract) - masks the
+    node id to it.  feat.bin is not opened (the reference's evaluation scripts use this to run shapes without one)."""
+    import torch
+    _drive(mode, dataset, *args,
+           env={"XG_TEST_NUM_GPU": str(max(1, torch.cuda.device_count())), "SAMGRAPH_EMPTY_FEAT": str(bits)})

@@ -153,7 +153,20 @@ struct Dataset {
   std::vector<uint32_t> ranking_owned;
   uint32_t *ranking_rw = nullptr;  // kCacheByPreSample: shared, written by worker 0 at sample_init
   std::vector<Mapping> maps;
-  size_t feat_row_bytes() const { return feat_dim * (feat_dtype == XG_F16 ? 2 : feat_dtype == XG_F64 ? 8 : feat_dtype == XG_U8 ? 1 : 4); }
+  // SAMGRAPH_EMPTY_FEAT = k (constant.cc kEnvEmptyFeat, run_config.cc:138): mock features - the host table has 2^k rows
+  // and node v reads row v & (2^k - 1) everywhere (engine.cc:198-208, cuda_extraction.cu:51-72)
+  unsigned empty_feat = 0;
+  size_t feat_table_rows() const { return empty_feat ? (size_t(1) << empty_feat) : num_node; }
+  uint32_t feat_row_mask() const { return empty_feat ? (uint32_t)((size_t(1) << empty_feat) - 1) : 0u; }
+  static size_t elem_bytes(int dtype) {  // GetDataTypeBytes, common.cc
+    switch (dtype) {
+      case XG_F16: return 2;
+      case XG_F64: case XG_I64: return 8;
+      case XG_U8: case XG_I8: return 1;
+      default: return 4;
+    }
+  }
+  size_t feat_row_bytes() const { return feat_dim * elem_bytes(feat_dtype); }
 };
 
 bool file_exists(const std::string &p) {
@@ -222,8 +235,25 @@ void load_dataset(Dataset &ds, const RunConfig &cfg, bool shared) {
   SAM_CHECK(ds.num_node < 0xFFFFFFFFull && ds.num_edge <= 0xFFFFFFFFull);  // IdType is 32-bit (constant.h:28)
   ds.indptr = static_cast<const uint32_t *>(map_file(ds, dir + "indptr.bin", (ds.num_node + 1) * 4, shared));
   ds.indices = static_cast<const uint32_t *>(map_file(ds, dir + "indices.bin", ds.num_edge * 4, shared));
-  SAM_CHECK_MSG(file_exists(dir + "feat.bin"), "feat.bin is missing (SAMGRAPH_EMPTY_FEAT mock features are not supported)");
-  ds.feat = map_file(ds, dir + "feat.bin", ds.num_node * ds.feat_row_bytes(), shared);
+  if (const char *ef = std::getenv("SAMGRAPH_EMPTY_FEAT")) ds.empty_feat = (unsigned)std::strtoul(ef, nullptr, 10);
+  SAM_CHECK_MSG(ds.empty_feat < 32, "SAMGRAPH_EMPTY_FEAT must be below 32");
+  if (ds.empty_feat) {
+    // Tensor::Empty of 2^k rows in the reference (engine.cc:198-213): contents undefined there; here a fixed byte
+    // pattern of the row number so that a run can be checked (byte i of row r = (31 r + i) & 0x3F: small finite
+    // values in every dtype).  Anonymous shared mapping: survives fork like the mapped files.
+    const size_t bytes = ds.feat_table_rows() * ds.feat_row_bytes();
+    void *mem = ::mmap(nullptr, std::max<size_t>(bytes, 4096), PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+    SAM_CHECK_MSG(mem != MAP_FAILED, "anonymous mmap failed for the mock feature table");
+    auto *b = static_cast<unsigned char *>(mem);
+    const size_t rb = ds.feat_row_bytes();
+    for (size_t r = 0; r < ds.feat_table_rows(); ++r)
+      for (size_t i = 0; i < rb; ++i) b[r * rb + i] = (unsigned char)((31 * r + i) & 0x3F);
+    ds.maps.push_back({mem, std::max<size_t>(bytes, 4096)});
+    ds.feat = mem;
+  } else {
+    SAM_CHECK_MSG(file_exists(dir + "feat.bin"), "feat.bin is missing: provide it or set SAMGRAPH_EMPTY_FEAT=k (2^k mock rows)");
+    ds.feat = map_file(ds, dir + "feat.bin", ds.num_node * ds.feat_row_bytes(), shared);
+  }
   SAM_CHECK_MSG(file_exists(dir + "label.bin"), "label.bin is missing");
   ds.label = static_cast<const int64_t *>(map_file(ds, dir + "label.bin", ds.num_node * 8, shared));
   ds.train_set = static_cast<const uint32_t *>(map_file(ds, dir + "train_set.bin", ds.num_train * 4, shared));
@@ -637,7 +667,9 @@ void build_feature_store(Engine &e) {
   const size_t V = ds.num_node;
   size_t n_cached = (size_t)(V * cfg.cache_percentage);
   if (n_cached > V) n_cached = V;
-  if (n_cached < V) e.store.host = pin_host(ds.feat, V * row_bytes);  // misses: zero-copy UVA loads
+  const size_t T = ds.feat_table_rows();  // rows of the host table: V, or 2^k with SAMGRAPH_EMPTY_FEAT=k
+  e.store.host_row_mask = ds.feat_row_mask();
+  if (n_cached < V) e.store.host = pin_host(ds.feat, T * row_bytes);  // misses: zero-copy UVA loads
   if (n_cached == 0) return;                                          // cache_table == NULL: every row from `host`
   const bool ics22 = cfg.run_arch == kArch6 && cfg.use_ics22_song_solver && e.shared != nullptr;
   const bool parted = (cfg.run_arch == kArch6 && cfg.part_cache && e.shared != nullptr) || ics22;
@@ -645,9 +677,9 @@ void build_feature_store(Engine &e) {
   if (!parted && n_cached == V) {
     // every row cached in one part: lay the part out by node id (where a cached row sits is ours to choose) and
     // skip the direct-address table - no 4-byte random lookup (a 128-byte DRAM line each) in front of every row
-    const void *h = pin_host(ds.feat, V * row_bytes);
-    void *d_all = dev_alloc(e, V * row_bytes);
-    SAM_CUDA(cudaMemcpyAsync(d_all, h, V * row_bytes, cudaMemcpyHostToDevice, e.stream));
+    const void *h = pin_host(ds.feat, T * row_bytes);
+    void *d_all = dev_alloc(e, T * row_bytes);
+    SAM_CUDA(cudaMemcpyAsync(d_all, h, T * row_bytes, cudaMemcpyHostToDevice, e.stream));
     SAM_CUDA(cudaStreamSynchronize(e.stream));
     e.store.host = d_all;  // "host" slot of the handle = the flat table, wherever it lives
     return;
@@ -669,7 +701,7 @@ void build_feature_store(Engine &e) {
     for (size_t r = 0; r < n_cached; ++r) table[ranks[r]] = (uint32_t)r;
     e.store.cache_table = to_device(e, table.data(), V);
   }
-  const void *h_feat = pin_host(ds.feat, V * row_bytes);
+  const void *h_feat = pin_host(ds.feat, T * row_bytes);
   e.store.num_part = P;
   auto gather_rows_to_device = [&](const uint32_t *ids, size_t n) -> void * {
     // CPUExtract + H2D in the reference; here the GPU gathers the rows straight out of the host mapping
@@ -678,7 +710,8 @@ void build_feature_store(Engine &e) {
       uint32_t *d_ids = nullptr;
       SAM_CUDA(cudaMalloc(&d_ids, n * sizeof(uint32_t)));
       SAM_CUDA(cudaMemcpyAsync(d_ids, ids, n * sizeof(uint32_t), cudaMemcpyHostToDevice, e.stream));
-      SAM_XG(xg_extract_miss_data(d_rows, h_feat, d_ids, nullptr, n, row_bytes, e.stream));
+      // CPUMockExtract when the table is a mock (dist_graph.cu:508-515), CPUExtract otherwise
+      SAM_XG(xg_mock_extract(d_rows, h_feat, d_ids, n, row_bytes, ds.empty_feat, e.stream));
       SAM_CUDA(cudaStreamSynchronize(e.stream));
       cudaFree(d_ids);
     }
@@ -965,6 +998,23 @@ bool sem_wait_or_shutdown(Engine &e, sem_t *sem) {
 
 inline uint64_t align256(uint64_t x) { return (x + 255) & ~255ull; }
 
+// Largest packed Task this sampler can produce: the caps xg_sampler_create derives from batch size and fanouts
+// (PredictNumNodes, common.cc:488-497, clipped to num_node + batch), every piece 256-byte aligned.
+size_t worst_case_task_bytes(const Engine &e) {
+  const RunConfig &cfg = g_cfg;
+  const size_t B = cfg.batch_size, L = cfg.num_layer;
+  size_t limit = B;
+  for (size_t i = L; i-- > 0;) limit += limit * cfg.fanout[i];
+  if (limit > e.ds.num_node + B) limit = e.ds.num_node + B;
+  size_t cur = B, bytes = align256(B * 4);
+  for (size_t i = L; i-- > 0;) {
+    const size_t cap_edge = cur * cfg.fanout[i];
+    bytes += 3 * align256(cap_edge * 4) + align256((cur + 1) * 4);  // row, col, data, csc_indptr
+    cur = std::min(cur + cap_edge, limit);
+  }
+  return bytes + align256(cur * 4) + 4096;
+}
+
 void send_task(Engine &e, const xg_batch_view &v, size_t epoch, double sample_time) {
   SAM_CHECK(e.queue != nullptr);
   TaskQueueBlock &q = *e.queue;
@@ -999,13 +1049,17 @@ void send_task(Engine &e, const xg_batch_view &v, size_t epoch, double sample_ti
   const unsigned k = e.next_stage++ % kStagePerSampler;
   if (!sem_wait_or_shutdown(e, &q.stage_free[s][k])) return;
   Engine::Stage &st = e.stages[k];
-  if (st.cap < d.bytes) {  // first use, or a batch larger than any before: (re)allocate with slack, export again
-    if (st.ptr) SAM_XG(xg_device_free(st.ptr));
-    st.cap = d.bytes + d.bytes / 4;
+  if (st.ptr == nullptr) {
+    // Allocated ONCE, at the worst-case packed size of a Task (the sampler's own buffer caps), and never freed or
+    // re-exported while the process lives: trainers keep the IPC mapping of a stage open for as long as they like
+    // (peer_stage[][]), and cudaFree of an exported region before every importer has closed it is undefined
+    // behaviour.  (r01 grew a stage on demand and freed the old block.)
+    st.cap = worst_case_task_bytes(e);
     SAM_XG(xg_device_malloc(&st.ptr, st.cap));  // 2 MiB granular: peer reads of smaller blocks crawl
     SAM_XG(xg_ipc_export(st.ptr, q.stage_ipc[s][k]));
     __atomic_add_fetch(&q.stage_gen[s][k], 1u, __ATOMIC_SEQ_CST);
   }
+  SAM_CHECK_MSG(d.bytes <= st.cap, "a packed Task is larger than the worst case computed from batch size and fanouts");
   for (const Piece &p : pieces)
     if (p.bytes)
       SAM_CUDA(cudaMemcpyAsync(static_cast<char *>(st.ptr) + p.off, p.src, p.bytes, cudaMemcpyDeviceToDevice, e.stream));
@@ -1701,7 +1755,7 @@ void samgraph_get_graph_tensor(uint64_t key, int which, int layer, samgraph_tens
     if (which == SAMGRAPH_TENSOR_DATASET_FEAT) {
       out->data = const_cast<void *>(e.ds.feat);
       out->ndim = 2;
-      out->shape[0] = (int64_t)e.ds.num_node;
+      out->shape[0] = (int64_t)e.ds.feat_table_rows();
       out->shape[1] = (int64_t)e.ds.feat_dim;
       out->dtype = e.ds.feat_dtype;
     } else {

@@ -99,6 +99,12 @@ __device__ __forceinline__ void split_rank(const xg_feature_store &st, uint32_t 
   }
 }
 
+// SAMGRAPH_EMPTY_FEAT mock features (cuda_extraction.cu:51-72, cuda_cache_manager_device.cu:589-592): the host table
+// has only 2^k rows and every host-row index is masked to it; 0 = no mask
+__device__ __forceinline__ uint32_t host_row(const xg_feature_store &st, uint32_t idx) {
+  return st.host_row_mask ? (idx & st.host_row_mask) : idx;
+}
+
 __device__ __forceinline__ const char *route_row(const xg_feature_store &st, int mode, uint32_t idx,
                                                  int *klass) {
   uint32_t rank = kEmpty;
@@ -106,7 +112,7 @@ __device__ __forceinline__ const char *route_row(const xg_feature_store &st, int
   else if (mode == kByNode && st.cache_table != nullptr) rank = lookup_rank(st, idx);
   if (rank == kEmpty) {
     *klass = 2;  // host (or the flat table when nothing is cached)
-    return static_cast<const char *>(st.host) + (size_t)idx * st.row_bytes;
+    return static_cast<const char *>(st.host) + (size_t)host_row(st, idx) * st.row_bytes;
   }
   if (rank < st.num_replicated) {
     *klass = 0;
@@ -176,7 +182,7 @@ gather_rows_kernel(const xg_feature_store st, int mode, const uint32_t *__restri
       if (mode == kCacheRank) rank = idx_cur;
       else if (by_table) rank = rank_cur;
       if (rank == kEmpty) {
-        sp = static_cast<const char *>(st.host) + (size_t)idx_cur * st.row_bytes;
+        sp = static_cast<const char *>(st.host) + (size_t)host_row(st, idx_cur) * st.row_bytes;
       } else if (rank < st.num_replicated) {
         klass = 0;
         sp = static_cast<const char *>(st.replica) + (size_t)rank * st.row_bytes;
@@ -283,7 +289,7 @@ gather_rows_ring_kernel(const xg_feature_store st, int mode, const uint32_t *__r
     uint32_t rank = kEmpty;
     if (mode == kCacheRank) rank = idx;
     else if (by_table) rank = rank_in;
-    if (rank == kEmpty) return static_cast<const char *>(st.host) + (size_t)idx * st.row_bytes;
+    if (rank == kEmpty) return static_cast<const char *>(st.host) + (size_t)host_row(st, idx) * st.row_bytes;
     if (rank < st.num_replicated) return static_cast<const char *>(st.replica) + (size_t)rank * st.row_bytes;
     rank -= st.num_replicated;
     uint32_t part, row;
@@ -449,14 +455,19 @@ int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx,
       const char *e = std::getenv("XG_GATHER_RING_STAGES");
       return e ? std::atoi(e) : 3;
     }();
+    int ring_dev = 0;
+    XG_CUDA(cudaGetDevice(&ring_dev));
     const size_t ring_ctas_needed = (groups + kRingWarps - 1) / kRingWarps;
     const unsigned grid = grid_for(ring_ctas_needed, ring_ctas);
 #define XG_RING(S)                                                                                                \
   do {                                                                                                            \
     const size_t smem = (size_t)kRingWarps * S * kStageChunks * sizeof(int4);                                     \
-    static const bool attr_set = cudaFuncSetAttribute(gather_rows_ring_kernel<S>,                                 \
-                                                      cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) == cudaSuccess; \
-    XG_REQUIRE(attr_set, "cannot reserve shared memory for the ring gather");                                     \
+    static bool attr_set[64] = {}; /* per DEVICE: a process may drive several GPUs */                            \
+    if (!attr_set[ring_dev & 63]) {                                                                               \
+      XG_REQUIRE(cudaFuncSetAttribute(gather_rows_ring_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize,    \
+                                      (int)smem) == cudaSuccess, "cannot reserve shared memory for the ring gather"); \
+      attr_set[ring_dev & 63] = true;                                                                             \
+    }                                                                                                             \
     gather_rows_ring_kernel<S><<<grid, kRingWarps * 32, smem, s>>>(st, mode, src_idx, dst_idx, num_rows,          \
                                                                    d_num_rows, cpr, o);                           \
   } while (0)
@@ -608,6 +619,17 @@ int xg_extract_ggms(const xg_feature_store *store, const uint32_t *d_nodes, size
   return launch_gather(*store, kByNode, d_nodes, nullptr, num_nodes, nullptr, d_out, d_stats, as_stream(stream));
 }
 
+int xg_mock_extract(void *d_dst, const void *src, const uint32_t *d_index, size_t num_index, size_t row_bytes,
+                    unsigned empty_feat_bits, void *stream) {
+  XG_REQUIRE(src != nullptr || num_index == 0, "src is NULL");
+  XG_REQUIRE(empty_feat_bits < 32, "empty_feat_bits must be below 32");
+  xg_feature_store st{};
+  st.host = src;
+  st.row_bytes = row_bytes;
+  st.host_row_mask = empty_feat_bits ? (uint32_t)((1ull << empty_feat_bits) - 1) : 0u;
+  return launch_gather(st, kHostRow, d_index, nullptr, num_index, nullptr, d_dst, nullptr, as_stream(stream));
+}
+
 int xg_extract_miss_data(void *d_out, const void *host_feat, const uint32_t *d_miss_src,
                          const uint32_t *d_miss_dst, size_t num_miss, size_t row_bytes, void *stream) {
   XG_REQUIRE(host_feat != nullptr, "host_feat is NULL");
@@ -713,25 +735,29 @@ extern "C" int xg_build_replica_words(const uint32_t *d_cache_table, uint32_t nu
   unsigned long long *mismatch = nullptr, h_mismatch[2] = {0, 0};
   void *temp = nullptr;
   size_t temp_bytes = 0;
-  XG_CUDA(cudaMalloc(&bits, (size_t)num_words * 3 * sizeof(uint32_t) + sizeof(unsigned long long) * 2));
+  // three u32 arrays of num_words, then (8-byte aligned) the two 64-bit mismatch counters
+  const size_t counter_word = ((size_t)num_words * 3 + 1) & ~(size_t)1;
+  XG_CUDA(cudaMalloc(&bits, counter_word * sizeof(uint32_t) + sizeof(unsigned long long) * 2));
   counts = bits + num_words;
   prefix = counts + num_words;
-  mismatch = reinterpret_cast<unsigned long long *>(bits + (size_t)((num_words * 3 + 1) & ~1u));
+  mismatch = reinterpret_cast<unsigned long long *>(bits + counter_word);
   cudaError_t e = cub::DeviceScan::ExclusiveSum(nullptr, temp_bytes, counts, prefix, (int)num_words, s);
   if (e == cudaSuccess) e = cudaMalloc(&temp, temp_bytes ? temp_bytes : 16);
   if (e == cudaSuccess) e = cudaMemsetAsync(mismatch, 0, 2 * sizeof(unsigned long long), s);
-  if (e == cudaSuccess) {
+  if (e == cudaSuccess) {  // every exit below goes through the common cleanup: nothing returns with temp / bits allocated
     const unsigned grid = grid_for(((size_t)num_words * 32 + 255) / 256, 8);
     replica_bits_kernel<<<grid, 256, 0, s>>>(d_cache_table, num_node, num_replicated, bits, counts, num_words);
-    XG_LAUNCHED();
-    e = cub::DeviceScan::ExclusiveSum(temp, temp_bytes, counts, prefix, (int)num_words, s);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cub::DeviceScan::ExclusiveSum(temp, temp_bytes, counts, prefix, (int)num_words, s);
     if (e == cudaSuccess) {
       replica_words_kernel<<<grid, 256, 0, s>>>(d_cache_table, num_node, bits, prefix, static_cast<uint2 *>(d_words), num_words,
                                                 num_replicated, mismatch);
-      XG_LAUNCHED();
-      e = cudaMemcpyAsync(h_mismatch, mismatch, sizeof(h_mismatch), cudaMemcpyDeviceToHost, s);
-      if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      e = cudaGetLastError();
     }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h_mismatch, mismatch, sizeof(h_mismatch), cudaMemcpyDeviceToHost, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   }
   cudaFree(temp);
   cudaFree(bits);

@@ -76,14 +76,17 @@ int xg_presample_rank(const uint32_t *d_freq, uint32_t num_node, uint32_t *d_ran
   if (e == cudaSuccess) e = cudaMalloc(&temp, temp_bytes ? temp_bytes : 16);
   if (e == cudaSuccess) {
     const unsigned grid = grid_for(((size_t)num_node + 255) / 256, 8);
+    // every exit goes through the cleanup below (no early return with temp / sorted / keys allocated)
     freq_pack_kernel<<<grid, 256, 0, s>>>(d_freq, keys, num_node);
-    XG_LAUNCHED();
-    e = cub::DeviceRadixSort::SortKeysDescending(temp, temp_bytes, keys, sorted, (int64_t)num_node, 0, 64, s);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cub::DeviceRadixSort::SortKeysDescending(temp, temp_bytes, keys, sorted, (int64_t)num_node, 0, 64, s);
     if (e == cudaSuccess) {
       freq_unpack_kernel<<<grid, 256, 0, s>>>(sorted, d_rank_nodes, d_rank_freq, num_node);
-      XG_LAUNCHED();
-      e = cudaStreamSynchronize(s);
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      e = cudaGetLastError();
     }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
   }
   cudaFree(temp);
   cudaFree(sorted);

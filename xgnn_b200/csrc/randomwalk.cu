@@ -177,10 +177,13 @@ int launch_random_walk(const xg_graph &g, const uint32_t *d_input, size_t num_in
   XG_REQUIRE(tiles <= scan.max_tiles, "scan workspace too small");
   const size_t smem = ((size_t)2 * kRwWarps * walk_length * num_walk + (size_t)2 * kRwTile * K) * sizeof(uint32_t);
   if (smem > 48 * 1024) {
-    static bool raised = false;
-    if (!raised) {
+    // the attribute is per DEVICE: a process that drives several GPUs must raise it on each of them
+    static bool raised[64] = {};
+    int dev = 0;
+    XG_CUDA(cudaGetDevice(&dev));
+    if (!raised[dev & 63]) {
       XG_CUDA(cudaFuncSetAttribute(random_walk_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
-      raised = true;
+      raised[dev & 63] = true;
     }
   }
   random_walk_topk_kernel<<<grid_for(tiles, 4), kRwBlock, smem, s>>>(

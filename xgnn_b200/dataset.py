@@ -109,9 +109,15 @@ def cache_rank_nodes(num_node: int, num_cached: int, num_replicated: int = 0) ->
 
 def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale: int = 1, cache_pct: float = 1.0,
                 replicate_pct: float = 0.0, with_features: bool = True, seed: int = SYNTH_SEED,
-                flat_when_full: bool = True, replica_words: bool = True) -> GGMSStore:
+                flat_when_full: bool = True, replica_words: bool = True, replicate_topology: bool = False,
+                empty_feat: int = 20) -> GGMSStore:
     """Generate THIS rank's shards (topology part `rank`, feature part `rank`) of the named shape,
-    scaled down by `scale`. Peer parts are attached afterwards (attach_peers) from IPC handles."""
+    scaled down by `scale`. Peer parts are attached afterwards (attach_peers) from IPC handles.
+    replicate_topology: every GPU keeps the whole CSR (B200 option: papers100M's 6.9 GB fits everywhere, so the sample
+    phase needs no NVLink; the reference's `v % P` sharding stays the default and is what config 3 asks for).
+    cache_pct < 1: the uncached rows live in pinned host memory; the host tier is a SAMGRAPH_EMPTY_FEAT-style mock table
+    of 2^empty_feat rows (node v reads row v & mask, cuda/cuda_extraction.cu:51-72), as the reference's evaluation
+    scripts run shapes whose feature file does not fit - the PCIe traffic is real, the host footprint small."""
     V, E, dim, dtype, num_class, train_frac = SHAPES[shape]
     V, E = V // scale, E // scale
     dev = torch.device("cuda", device)
@@ -120,9 +126,12 @@ def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale
     st = GGMSStore(num_node=V, num_edge=0, dim=dim, dtype=dtype, num_class=num_class, rank=rank, world=world)
     with torch.cuda.device(dev):
         # topology: use_dist_graph = 1.0 -> num_cache_node = V, every node lives in some GPU part
-        n_part = (V - rank + P - 1) // P
-        indptr, indices, ne = gen_csr(rank, P, n_part, V, c, seed, dev)
-        st.local.update(indptr=indptr, indices=indices, num_local_edge=ne)
+        if replicate_topology:
+            indptr, indices, ne = gen_csr(0, 1, V, V, c, seed, dev)
+        else:
+            n_part = (V - rank + P - 1) // P
+            indptr, indices, ne = gen_csr(rank, P, n_part, V, c, seed, dev)
+        st.local.update(indptr=indptr, indices=indices, num_local_edge=ne, replicate_topology=replicate_topology)
         st.label = (torch.arange(V, dtype=torch.int64, device=dev) % num_class)
         if with_features and P == 1 and cache_pct >= 1.0 and flat_when_full:
             # one part holding every row: WHERE a cached row is stored is ours to choose ("GGMS routing must
@@ -147,6 +156,15 @@ def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale
             st.local["feat_part"] = gen_features(max(mine.numel(), 1), dim, dtype, dev, row_ids=mine if mine.numel() else None)
             st.local["num_cached"] = n_cached
             st.local["num_replicated"] = n_rep
+            if n_cached < V:  # cold tier: pinned host memory, read over PCIe through UVA
+                rows = 1 << empty_feat
+                host = torch.empty((rows, dim), dtype=dtype).pin_memory()
+                step = max(1, (256 << 20) // st.row_bytes)
+                for o in range(0, rows, step):
+                    n = min(step, rows - o)
+                    host[o:o + n].copy_(gen_features(n, dim, dtype, dev, begin=o))
+                st.local["host_feat"] = host
+                st.local["empty_feat"] = empty_feat
             if n_rep:  # ranks [0, n_rep) are nodes 0..n_rep-1 in policy order: every GPU generates its own copy
                 hot = torch.from_numpy(np.ascontiguousarray(ranks[:n_rep]).view(np.int32)).to(dev)
                 st.local["replica"] = gen_features(n_rep, dim, dtype, dev, row_ids=hot)
@@ -163,10 +181,14 @@ def attach(st: GGMSStore, part_indptr=None, part_indices=None, feat_parts=None, 
     """Fill the by-value handles. With world == 1 the local shards are the whole store; otherwise the
     caller passes every part's pointer (local tensor or IPC-mapped peer address) in part order."""
     P = st.world
-    if part_indptr is None:
-        assert P == 1
+    if st.local.get("replicate_topology") or part_indptr is None:
+        assert P == 1 or st.local.get("replicate_topology")
         part_indptr, part_indices = [st.local["indptr"]], [st.local["indices"]]
+    if feat_parts is None:
+        assert P == 1
         feat_parts = [st.local.get("feat_part")]
+    if host_feat is None:
+        host_feat = st.local.get("host_feat")
     st.graph = ops.make_graph(part_indptr=part_indptr, part_indices=part_indices, num_cache_node=st.num_node,
                               num_node=st.num_node, host_indptr=None, host_indices=None)
     if st.local.get("flat"):
@@ -175,5 +197,6 @@ def attach(st: GGMSStore, part_indptr=None, part_indices=None, feat_parts=None, 
         st.store = ops.make_feature_store(st.row_bytes, host_feat, st.local["cache_table"], parts=feat_parts,
                                           local_parts=(st.rank,), replica=st.local.get("replica"),
                                           num_replicated=st.local.get("num_replicated", 0),
-                                          replica_words=st.local.get("replica_words"))
+                                          replica_words=st.local.get("replica_words"),
+                                          empty_feat=st.local.get("empty_feat", 0) if host_feat is not None else 0)
     return st

@@ -207,11 +207,24 @@ def GPUExtract(src: torch.Tensor | int, index: torch.Tensor, dim: int | None = N
     return out
 
 
+def GPUMockExtract(src: torch.Tensor, index: torch.Tensor, empty_feat: int) -> torch.Tensor:
+    """cuda::GPUMockExtract (cuda/cuda_extraction.cu:118-160): out[i] = src[index[i] & (2^empty_feat - 1)]"""
+    dim = src.shape[1] if src.dim() == 2 else 1
+    out = torch.empty((index.numel(),) + tuple(src.shape[1:]), dtype=src.dtype, device=index.device)
+    check(lib.xg_mock_extract(_ptr(out), src.data_ptr(), _ptr(_ids(index)), index.numel(), dim * src.element_size(),
+                              empty_feat, _stream()))
+    return out
+
+
 def make_feature_store(row_bytes: int, host: torch.Tensor | int | None, cache_table: torch.Tensor | None = None,
                        parts=None, local_parts=(), replica=None, num_replicated: int = 0,
-                       compact_bitwidth: int = 0, replica_words: torch.Tensor | None = None) -> XgFeatureStore:
-    """DeviceDistFeature + cache table + host table in one handle (cuda/dist_graph.h:182-213)."""
+                       compact_bitwidth: int = 0, replica_words: torch.Tensor | None = None,
+                       empty_feat: int = 0) -> XgFeatureStore:
+    """DeviceDistFeature + cache table + host table in one handle (cuda/dist_graph.h:182-213).
+    empty_feat = k > 0: SAMGRAPH_EMPTY_FEAT mock features - `host` holds 2^k rows and host-resident node v reads row
+    v & (2^k - 1) (cuda/cuda_extraction.cu:51-72)."""
     st = XgFeatureStore()
+    st.host_row_mask = ((1 << empty_feat) - 1) if empty_feat else 0
 
     def p(x):
         return x if isinstance(x, int) or x is None else x.data_ptr()
@@ -409,6 +422,16 @@ class MinibatchSampler:
         if isinstance(seeds, torch.Tensor):
             on_dev = 1 if seeds.is_cuda else 0
             ptr, n = seeds.data_ptr(), seeds.numel()
+            if on_dev and n:
+                # the engine copies the seeds on ITS stream: order that copy after whatever produced the tensor on
+                # torch's current stream, and keep the caching allocator from reusing the memory before the copy ran
+                mine = getattr(self, "_sample_stream", None)
+                if mine is None:
+                    mine = self._sample_stream = torch.cuda.ExternalStream(self.stream_ptr, device=seeds.device)
+                cur = torch.cuda.current_stream(seeds.device)
+                if cur.cuda_stream != mine.cuda_stream:
+                    mine.wait_stream(cur)
+                    seeds.record_stream(mine)
         else:
             on_dev, ptr, n = 0, seeds.ctypes.data, len(seeds)
         check(lib.xg_sampler_submit(self._h, ptr, n, on_dev, batch_key, byref(b)))
