@@ -220,7 +220,8 @@ def main():
         background = len(sys.argv) > 4 and sys.argv[4] == "bg"
         fan = run_config(sam, d, sample_type, g, sam.kArch3, {"sampler_ctx": "cuda:0", "trainer_ctx": "cuda:0"})
         sam.init()
-        assert tuple(sam.get_dataset_feat().shape) == (g["V"], g["dim"])
+        k = int(os.environ.get("SAMGRAPH_EMPTY_FEAT", "0"))  # mock features: the table has 2^k rows (engine.cc:198-208)
+        assert tuple(sam.get_dataset_feat().shape) == ((1 << k) if k else g["V"], g["dim"])
         assert np.array_equal(sam.get_dataset_label().numpy(), g["label"])
         consume(sam, g, fan, sample_type, 0, 1, background)
         print("DRIVER OK")

@@ -469,9 +469,8 @@ def test_extract_two_tier_rank_select_words(P, pct, rep):
         assert lib.xg_build_replica_words(dev(policy_table).data_ptr(), V, nrep, bad.data_ptr(), None, None) != 0
 
 
-@gpu
 @pytest.mark.parametrize("dtype,dim,bits", [(np.float32, 128, 8), (np.float16, 768, 4), (np.float32, 100, 1), (np.uint8, 16, 12)])
-def test_mock_extract_matches_oracle(dtype, dim, bits):
+def test_mock_extract_matches_oracle(ops, dtype, dim, bits):
     """GPUMockExtract (cuda/cuda_extraction.cu:51-72,118-160) == CPUMockExtract restatement, byte for byte; and through
     the GGMS store: host-resident rows are masked, cached rows are whatever the cache was built with"""
     import torch

@@ -47,9 +47,13 @@ def _worker(rank, world, port, V, n_train, batch, replicate):
         from xgnn_b200 import dataset as D
         from xgnn_b200._clib import check, lib
 
-        # ---- work split: bench.epoch_order (numpy shuffle) and the engine's aligned shuffler (C-ABI) ----
+        # ---- work split: bench.AlignedShuffler (what bench.py's epochs use) and the engine's routine (C-ABI) ----
         train = D.train_set(V, n_train)
-        mine = bench.epoch_order(train, 3, rank, world)
+        sh = bench.AlignedShuffler(train, rank, world, batch)
+        for _ in range(3):
+            epoch_batches = sh.next_epoch()
+        mine = np.concatenate(epoch_batches)
+        assert all(len(b) == batch for b in epoch_batches[:-1]) and len(epoch_batches) == sh.steps
         parts = _gather_arrays(mine, world)
         assert len({len(p) for p in parts}) == 1, "slices must be equal (aligned shuffler pads to a multiple of P)"
         allv = np.concatenate(parts)
