@@ -566,7 +566,7 @@ def sampler_kw(args):
     return kw
 
 
-STAGES = {"reset_seeds": 0, "sample": 1, "number": 2, "input_nodes": 4, "feature": 5, "label": 6}
+STAGES = {"reset_seeds": 0, "sample": 1, "insert": 2, "number": 3, "input_nodes": 4, "feature": 5, "label": 6}
 
 
 def stage_pass(R, args):
@@ -589,9 +589,9 @@ def stage_pass(R, args):
         mb = sm2.wait(hnd)
         ms = ctypes.c_float(0)
         for name, code in STAGES.items():
-            for l in (range(L) if code in (1, 2) else [0]):
+            for l in (range(L) if code in (1, 2, 3) else [0]):
                 check(lib.xg_batch_stage_ms(hnd, code, l, ctypes.byref(ms)))
-                key = f"{name}.L{l}" if code in (1, 2) else name
+                key = f"{name}.L{l}" if code in (1, 2, 3) else name
                 acc[key] = acc.get(key, 0.0) + ms.value
         for l in range(L):
             info["edges"][l] += mb.num_edge[l]
@@ -635,6 +635,7 @@ def summarize(R, args, stage_ms, info):
     alg = {"feature": info["rows"] * (2 * row_bytes + 4), "label": info["seeds"] * (2 * 8 + 4)}
     for l in range(L):
         alg[f"sample.L{l}"] = info["inputs"][l] * 8 + info["edges"][l] * 12
+        # unique + remap (insert + number passes together): E * 16 + U * 4; quoted on the numbering pass
         alg[f"number.L{l}"] = info["edges"][l] * 16 + (info["inputs"][l - 1] - info["inputs"][l] if l > 0 else
                                                       info["rows"] - info["inputs"][0]) * 4
     stages = {}

@@ -244,9 +244,9 @@ int xg_combine_cache_data(void *d_out, const xg_feature_store *store, const uint
 /* stages of one minibatch, for xg_batch_stage_ms */
 enum {
   XG_STAGE_RESET_SEEDS = 0, /* Reset + FillWithDupRevised(seeds) */
-  XG_STAGE_SAMPLE = 1,      /* per layer: sample kernel (with the fused hash insert) */
-  XG_STAGE_NUMBER = 2,      /* per layer: number first occurrences (unique list append) */
-  XG_STAGE_REMAP = 3,       /* per layer: neighbour local ids */
+  XG_STAGE_SAMPLE = 1,      /* per layer: sample kernel */
+  XG_STAGE_INSERT = 2,      /* per layer: every sampled neighbour into the hash table (first occurrence wins) */
+  XG_STAGE_NUMBER = 3,      /* per layer: number first occurrences (unique list append) + neighbour local ids */
   XG_STAGE_INPUT_NODES = 4, /* input_nodes copy + counts */
   XG_STAGE_FEATURE = 5,     /* routed feature gather */
   XG_STAGE_LABEL = 6,       /* label gather */

@@ -2,7 +2,7 @@
 # A/B harness: runs bench.py once per environment assignment given as arguments ("" = default) and prints ms/step + stages.
 # usage (on the GPU box): tools/ab.sh "" "XG_TABLE_PERSIST_MB=64" ...
 for cfg in "$@"; do
-  out=$(env $cfg python bench.py --steps 60 --warmup 10 --no-cpu-baseline --stage-steps 10 2>/dev/null | tail -1)
+  out=$(env $cfg python bench.py --steps 60 --warmup 10 --no-cpu-baseline --no-secondary --stage-steps 10 2>/dev/null | tail -1)
   python - "$cfg" <<PY
 import json,sys
 d=json.loads('''$out''')

@@ -22,27 +22,50 @@ __device__ __forceinline__ uint64_t resolve_n(size_t n_max, const uint64_t *d_n)
   return n < n_max ? n : n_max;
 }
 
+// kInsertItems keys per thread: all home-slot CASes are issued before any result is consumed, so a thread has that
+// many independent L2 atomics in flight (the kernel is a stream of coalesced key loads + one random atomic per key).
+constexpr int kInsertItems = 4;
 __global__ void __launch_bounds__(256)
-table_insert_kernel(TableView t, const uint32_t *keys, uint32_t *pos_out,  // may alias (DupMutable)
+table_insert_kernel(TableView t, const uint32_t *__restrict__ keys, uint32_t *__restrict__ pos_out,
                     size_t n_max, const uint64_t *d_n) {
   const uint64_t n = resolve_n(n_max, d_n);
-  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n;
-       i += (uint64_t)gridDim.x * blockDim.x) {
-    pos_out[i] = table_insert(t, keys[i], kPosTag | (uint32_t)i);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i0 = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i0 < n; i0 += stride * kInsertItems) {
+    uint32_t key[kInsertItems], p[kInsertItems], old[kInsertItems];
+#pragma unroll
+    for (int k = 0; k < kInsertItems; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * stride;
+      key[k] = i < n ? keys[i] : 0u;
+    }
+#pragma unroll
+    for (int k = 0; k < kInsertItems; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * stride;
+      if (i < n) {
+        p[k] = table_home(t, key[k]);
+        old[k] = atomicCAS(&t.slots[p[k]], kEmpty, kPosTag | (uint32_t)i);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kInsertItems; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * stride;
+      if (i < n) pos_out[i] = table_insert_resolve(t, keys, key[k], kPosTag | (uint32_t)i, p[k], old[k]);
+    }
   }
 }
 
-// FillWithUnique: the caller vouches for uniqueness, so item i simply becomes local id base + i.
+// FillWithUnique: the caller vouches for uniqueness, so item i simply becomes local id base + i - once every key sits
+// in its slot (a probe must be able to read the key of any occupied slot, and that key is keys[pos] until n2o has it).
 __global__ void __launch_bounds__(256)
-table_fill_unique_kernel(TableView t, const uint32_t *__restrict__ keys, size_t n, int fill) {
+table_number_unique_kernel(TableView t, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ pos, size_t n,
+                           int fill) {
   const uint32_t base = t.items[fill - 1];
   for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n;
        i += (uint64_t)gridDim.x * blockDim.x) {
-    const uint32_t key = keys[i];
     const uint32_t local = base + (uint32_t)i;
-    uint32_t p = table_insert(t, key, local);  // local < 2^31 < any tag: atomicMin keeps it
+    const uint32_t p = pos[i];
     if (p != kEmpty && local < t.n2o_cap) {
-      t.n2o[local] = key;
+      t.slots[p] = local;
+      t.n2o[local] = keys[i];
       t.n2o_slot[local] = p;
     } else {
       *t.overflow = 1;
@@ -55,9 +78,9 @@ table_fill_unique_kernel(TableView t, const uint32_t *__restrict__ keys, size_t 
 // Tiles are handed out by a ticket so that the chained scan's ordering requirement holds for any
 // grid size.
 __global__ void __launch_bounds__(kAssignBlock)
-table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, uint32_t *__restrict__ local_out, size_t n_max,
-                    const uint64_t *d_n,
-                    int fill, uint32_t *ticket, uint64_t *scan_state) {
+table_assign_kernel(TableView t, const uint32_t *__restrict__ keys, const uint32_t *__restrict__ pos,
+                    uint32_t *__restrict__ local_out, size_t n_max, const uint64_t *d_n,
+                    int fill, bool ids_into_table, uint32_t *ticket, uint64_t *scan_state) {
   __shared__ uint32_t s_tile;
   __shared__ uint32_t s_cnt[kAssignItems * (kAssignBlock / 32)];
   __shared__ uint64_t s_tile_prefix;
@@ -81,7 +104,7 @@ table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, uint32_t *__r
     const uint64_t tile_base = (uint64_t)tile * kAssignTile;
 
     uint32_t slot_pos[kAssignItems];
-    uint2 slot[kAssignItems];
+    uint32_t word[kAssignItems];
     bool first[kAssignItems];
     uint32_t before[kAssignItems];  // flags before me inside my (row, warp)
 #pragma unroll
@@ -92,9 +115,9 @@ table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, uint32_t *__r
 #pragma unroll
     for (int k = 0; k < kAssignItems; ++k) {
       const uint64_t e = tile_base + (uint64_t)k * kAssignBlock + threadIdx.x;
-      slot[k] = make_uint2(kEmpty, 0);
-      if (slot_pos[k] != kEmpty) slot[k] = t.slots[slot_pos[k]];
-      first[k] = slot_pos[k] != kEmpty && slot[k].y == (kPosTag | (uint32_t)e);
+      word[k] = kEmpty;
+      if (slot_pos[k] != kEmpty) word[k] = t.slots[slot_pos[k]];
+      first[k] = slot_pos[k] != kEmpty && word[k] == (kPosTag | (uint32_t)e);
       const unsigned b = __ballot_sync(0xffffffffu, first[k]);
       before[k] = __popc(b & ((1u << lane) - 1));
       if (lane == 0) s_cnt[k * kWarps + warp] = __popc(b);
@@ -123,46 +146,64 @@ table_assign_kernel(TableView t, const uint32_t *__restrict__ pos, uint32_t *__r
 #pragma unroll
     for (int k = 0; k < kAssignItems; ++k) {
       if (first[k]) {
+        const uint64_t e = tile_base + (uint64_t)k * kAssignBlock + threadIdx.x;
         const uint32_t local = tile_first_local + s_cnt[k * kWarps + warp] + before[k];
         if (local < t.n2o_cap) {
-          t.slots[slot_pos[k]].y = local;
-          t.n2o[local] = slot[k].x;
+          t.n2o[local] = keys[e];  // nothing probes while this pass runs: the next insert kernel starts after it
           t.n2o_slot[local] = slot_pos[k];
+          // the id goes into the slot for the fills that follow; the LAST fill of a batch has no follower (the next
+          // thing that touches the table is Reset, which finds the slot through n2o_slot), so its ~4 M scattered
+          // stores - a fifth of the layer's random accesses - are skipped
+          if (ids_into_table) t.slots[slot_pos[k]] = local;
         } else {
           *t.overflow = 1;
-          t.slots[slot_pos[k]].y = kPosTag - 1;  // numbered "out of range": releases the waiters below; the batch is discarded
+          t.slots[slot_pos[k]] = kPosTag - 1;  // numbered "out of range"; the batch is discarded
         }
-        slot[k].y = local;
+        word[k] = local;
       }
     }
     __syncthreads();  // s_tile / s_cnt are reused by the next tile; this tile's local ids are visible CTA-wide
     if (local_out != nullptr) {
       // Fused remap (GPUMapEdges for the dst side): every position gets the local id of its key in the same pass.
-      // A later occurrence whose slot still holds a tagged position waits for the FIRST occurrence to be numbered:
-      // that one sits at a smaller position, i.e. in this tile (already written, see the barrier above) or in a tile
-      // with a smaller ticket, which is running or done and never waits on a later tile - so the wait terminates.
+      // A later occurrence whose slot still held a tagged position when this tile loaded it (its FIRST occurrence sits
+      // in a tile that is being numbered right now) cannot know the id yet: it stores the tagged word as a "pending"
+      // mark and table_remap_pending_kernel resolves it after this pass.  (r01 spun on the slot here; with ~1200 tiles
+      // in flight that parked whole CTAs behind their slowest lane: stalled_barrier 96 per issue.)
 #pragma unroll
       for (int k = 0; k < kAssignItems; ++k) {
         const uint64_t e = tile_base + (uint64_t)k * kAssignBlock + threadIdx.x;
-        if (e >= n) continue;
-        uint32_t v = kEmpty;
-        if (slot_pos[k] != kEmpty) {
-          v = slot[k].y;
-          if (v >= kPosTag) {
-            const volatile uint32_t *vp = &t.slots[slot_pos[k]].y;
-            while ((v = *vp) >= kPosTag) __nanosleep(20);
-          }
-        }
-        local_out[e] = v;
+        if (e < n) local_out[e] = word[k];  // local id | pending (>= kPosTag) | kEmpty (table overflow)
       }
     }
   }
 }
 
-// Reset.  The reference bumps a version word (cuda_hashtable.cu:739-742); 8-byte slots have no room for
+// second half of the fused remap: a position left "pending" by the numbering pass carries 0x80000000 | e', the
+// position of its key's FIRST occurrence - whose own entry of local_out is final (a first occurrence is never
+// pending), so the id is read from there: a 17 MB array instead of the table.  Four positions per thread.
+__global__ void __launch_bounds__(256)
+table_remap_pending_kernel(uint32_t *__restrict__ local_out, size_t n_max, const uint64_t *d_n) {
+  const uint64_t n = resolve_n(n_max, d_n);
+  const uint64_t n4 = n / 4;
+  uint4 *out4 = reinterpret_cast<uint4 *>(local_out);
+  auto fix = [&](uint32_t v) { return (v >= kPosTag && v != kEmpty) ? local_out[v & ~kPosTag] : v; };
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n4; i += (uint64_t)gridDim.x * blockDim.x) {
+    uint4 v = out4[i];
+    if ((v.x | v.y | v.z | v.w) & kPosTag) {
+      v.x = fix(v.x); v.y = fix(v.y); v.z = fix(v.z); v.w = fix(v.w);
+      out4[i] = v;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+    const uint64_t i = n4 * 4 + threadIdx.x;
+    local_out[i] = fix(local_out[i]);
+  }
+}
+
+// Reset.  The reference bumps a version word (cuda_hashtable.cu:739-742); 4-byte slots have no room for
 // one.  Two ways, chosen on the device from the number of ids the finished batch numbered:
-//   few ids  -> free exactly those slots (one scattered 8-byte store per id, n2o_slot remembers where);
-//   many ids -> stream 0xFF over the whole table with 16-byte stores: cap * 8 bytes at copy bandwidth
+//   few ids  -> free exactly those slots (one scattered 4-byte store per id, n2o_slot remembers where);
+//   many ids -> stream 0xFF over the whole table with 16-byte stores: cap * 4 bytes at copy bandwidth
 //               beats one random sector per id, and it leaves the (L2-sized) table resident in L2 for
 //               the inserts that follow.
 __global__ void __launch_bounds__(256)
@@ -170,13 +211,13 @@ table_clear_kernel(TableView t, int fill) {
   const uint32_t n = min(t.items[fill], t.n2o_cap);
   const uint64_t tid = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
   const uint64_t nthr = (uint64_t)gridDim.x * blockDim.x;
-  if ((uint64_t)n * 8 >= t.cap) {
+  if ((uint64_t)n * 8 >= t.cap) {  // ~32 bytes of L2 traffic per scattered 4-byte store vs 4 streamed bytes per slot
     uint4 *p = reinterpret_cast<uint4 *>(t.slots);
-    const uint64_t n4 = t.cap / 2;  // cap is even
+    const uint64_t n4 = t.cap / 4;  // cap is a multiple of 4
     const uint4 free4 = make_uint4(kEmpty, kEmpty, kEmpty, kEmpty);
     for (uint64_t i = tid; i < n4; i += nthr) p[i] = free4;
   } else {
-    for (uint64_t i = tid; i < n; i += nthr) t.slots[t.n2o_slot[i]] = make_uint2(kEmpty, kEmpty);
+    for (uint64_t i = tid; i < n; i += nthr) t.slots[t.n2o_slot[i]] = kEmpty;
   }
 }
 
@@ -187,7 +228,7 @@ table_gather_local_kernel(TableView t, const uint32_t *__restrict__ pos, uint32_
   for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n;
        i += (uint64_t)gridDim.x * blockDim.x) {
     const uint32_t p = pos[i];
-    out[i] = (p == kEmpty) ? kEmpty : t.slots[p].y;
+    out[i] = (p == kEmpty) ? kEmpty : t.slots[p];
   }
 }
 
@@ -200,7 +241,7 @@ table_lookup_kernel(TableView t, const uint32_t *__restrict__ in0, uint32_t *__r
   for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n;
        i += (uint64_t)gridDim.x * blockDim.x) {
     const uint32_t p = table_find(t, in[i]);
-    out[i] = (p == kEmpty) ? kEmpty : t.slots[p].y;
+    out[i] = (p == kEmpty) ? kEmpty : t.slots[p];
   }
 }
 
@@ -209,18 +250,25 @@ table_lookup_kernel(TableView t, const uint32_t *__restrict__ in0, uint32_t *__r
 int launch_table_insert(const TableView &t, const uint32_t *keys, uint32_t *pos_out, size_t n_max,
                         const uint64_t *d_n, cudaStream_t s) {
   if (n_max == 0) return XG_OK;
-  table_insert_kernel<<<grid_for((n_max + 255) / 256, 8), 256, 0, s>>>(t, keys, pos_out, n_max, d_n);
+  table_insert_kernel<<<grid_for((n_max + 256 * kInsertItems - 1) / (256 * kInsertItems), 8), 256, 0, s>>>(t, keys, pos_out, n_max,
+                                                                                                           d_n);
   XG_LAUNCHED();
   return XG_OK;
 }
 
-int launch_table_assign(const TableView &t, const uint32_t *pos, size_t n_max, const uint64_t *d_n,
-                        int fill, const ScanSpace &scan, cudaStream_t s, uint32_t *local_out) {
+int launch_table_assign(const TableView &t, const uint32_t *keys, const uint32_t *pos, size_t n_max, const uint64_t *d_n,
+                        int fill, const ScanSpace &scan, cudaStream_t s, uint32_t *local_out, bool ids_into_table) {
   size_t tiles = (n_max + kAssignTile - 1) / kAssignTile;
   XG_REQUIRE(tiles <= scan.max_tiles, "scan workspace too small");
-  table_assign_kernel<<<grid_for(tiles, 8), kAssignBlock, 0, s>>>(t, pos, local_out, n_max, d_n, fill, scan.ticket,
-                                                                  scan.state);
+  XG_REQUIRE(ids_into_table || local_out != nullptr, "a fill that leaves no ids in the table must hand them out");
+  table_assign_kernel<<<grid_for(tiles, 8), kAssignBlock, 0, s>>>(t, keys, pos, local_out, n_max, d_n, fill, ids_into_table,
+                                                                  scan.ticket, scan.state);
   XG_LAUNCHED();
+  if (local_out != nullptr && n_max > 0) {
+    XG_REQUIRE((reinterpret_cast<uintptr_t>(local_out) & 15) == 0, "local_out must be 16-byte aligned");
+    table_remap_pending_kernel<<<grid_for((n_max + 1023) / 1024, 8), 256, 0, s>>>(local_out, n_max, d_n);
+    XG_LAUNCHED();
+  }
   return XG_OK;
 }
 
@@ -323,7 +371,7 @@ int fill_dup(xg_hashtable *t, const uint32_t *d_input, uint32_t *pos, size_t n, 
   XG_CUDA(cudaMemsetAsync(t->scan_mem, 0, (tiles + 2) * sizeof(uint64_t), s));
   rc = launch_table_insert(t->view, d_input, pos, n, nullptr, s);
   if (rc) return rc;
-  return launch_table_assign(t->view, pos, n, nullptr, t->fill, scan_space(t), s);
+  return launch_table_assign(t->view, d_input, pos, n, nullptr, t->fill, scan_space(t), s);
 }
 
 int check_overflow(xg_hashtable *t, cudaStream_t s) {
@@ -361,23 +409,24 @@ int xg_hashtable_create(xg_hashtable **out, size_t max_items, int device) {
   auto *t = new xg_hashtable();
   t->device = device;
   t->max_items = max_items;
-  // slots per item: 1.25 by default.  The reference takes 2-4 (cuda_hashtable.cu:146-149) in 16-byte
-  // buckets; here the worst-case batch of the headline config (8.45 M ids) must stay inside the 126 MB
-  // L2 (84 MB at 1.25), because every probe is a random access and an L2 hit costs a third of a DRAM
-  // miss.  A typical batch fills 45 % of that.  XG_TABLE_SLOTS_PCT overrides (>= 110).
-  size_t pct = 125;
+  // slots per item: 1.5 by default.  The reference takes 2-4 (cuda_hashtable.cu:146-149) in 16-byte buckets; here the
+  // worst-case batch of the headline config (8.45 M ids) gives 51 MB of 4-byte slots, inside the part of the 126 MB
+  // L2 a randomly probed table can really use (~64 MB, tools/table_size_probe.py): every probe is a random access
+  // and an L2 hit costs a third of a DRAM miss.  A typical batch fills 39 % of that.  XG_TABLE_SLOTS_PCT overrides
+  // (>= 110).
+  size_t pct = 150;
   if (const char *e = std::getenv("XG_TABLE_SLOTS_PCT")) pct = std::strtoul(e, nullptr, 10);
   if (pct < 110) pct = 110;
-  t->capacity = (max_items * pct / 100 + 1024) & ~(size_t)1;
+  t->capacity = (max_items * pct / 100 + 1024) & ~(size_t)3;
   XG_REQUIRE(t->capacity < (1ull << 32), "table too large");
-  XG_CUDA(cudaMalloc(&t->view.slots, t->capacity * sizeof(uint2)));
+  XG_CUDA(cudaMalloc(&t->view.slots, t->capacity * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&t->view.n2o, max_items * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&t->view.n2o_slot, max_items * sizeof(uint32_t)));
   XG_CUDA(cudaMalloc(&t->view.items, (kMaxFills + 2) * sizeof(uint32_t)));
   t->view.overflow = t->view.items + kMaxFills + 1;
   t->view.cap = static_cast<uint32_t>(t->capacity);
   t->view.n2o_cap = static_cast<uint32_t>(max_items);
-  XG_CUDA(cudaMemset(t->view.slots, 0xFF, t->capacity * sizeof(uint2)));
+  XG_CUDA(cudaMemset(t->view.slots, 0xFF, t->capacity * sizeof(uint32_t)));
   XG_CUDA(cudaMemset(t->view.items, 0, (kMaxFills + 2) * sizeof(uint32_t)));
   *out = t;
   return XG_OK;
@@ -401,7 +450,7 @@ int xg_hashtable_reset(xg_hashtable *t, void *stream) {
   DeviceGuard guard(t->device);
   cudaStream_t s = as_stream(stream);
   if (t->dirty_full) {
-    XG_CUDA(cudaMemsetAsync(t->view.slots, 0xFF, t->capacity * sizeof(uint2), s));
+    XG_CUDA(cudaMemsetAsync(t->view.slots, 0xFF, t->capacity * sizeof(uint32_t), s));
     XG_CUDA(cudaMemsetAsync(t->view.items, 0, (kMaxFills + 2) * sizeof(uint32_t), s));
     t->dirty_full = false;
   } else {
@@ -419,12 +468,15 @@ int xg_hashtable_fill_with_unique(xg_hashtable *t, const uint32_t *d_input, size
   if (num_input == 0) return XG_OK;
   DeviceGuard guard(t->device);
   cudaStream_t s = as_stream(stream);
-  int rc = fold_fills(t, s);
+  int rc = ensure_scratch(t, num_input);
   if (rc) return rc;
+  if ((rc = fold_fills(t, s))) return rc;
   t->fill += 1;
   t->last_stream = s;
-  table_fill_unique_kernel<<<grid_for((num_input + 255) / 256, 8), 256, 0, s>>>(t->view, d_input,
-                                                                              num_input, t->fill);
+  // every key into its slot first (positions tagged), then number them: local id = base + position
+  if ((rc = launch_table_insert(t->view, d_input, t->scratch, num_input, nullptr, s))) return rc;
+  table_number_unique_kernel<<<grid_for((num_input + 255) / 256, 8), 256, 0, s>>>(t->view, d_input, t->scratch,
+                                                                                num_input, t->fill);
   XG_LAUNCHED();
   return XG_OK;
 }
@@ -446,8 +498,9 @@ int xg_hashtable_fill_with_dup_mutable(xg_hashtable *t, uint32_t *d_input, size_
   DeviceGuard guard(t->device);
   int rc = ensure_scratch(t, num_input);
   if (rc) return rc;
-  // the slot positions overwrite the input in place: no scratch traffic
-  return fill_dup(t, d_input, d_input, num_input, as_stream(stream));
+  // (the r01 table let the slot positions overwrite the input in place; keys are now read back through their
+  // positions while the fill is in flight, so the input stays intact and the positions go to the scratch array)
+  return fill_dup(t, d_input, t->scratch, num_input, as_stream(stream));
 }
 
 int xg_hashtable_fill_with_duplicates(xg_hashtable *t, const uint32_t *d_input, size_t num_input,

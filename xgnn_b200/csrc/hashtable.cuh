@@ -4,20 +4,25 @@
 // (reference: samgraph/common/cuda/cuda_hashtable.h:35-101, cuda_hashtable.cu:36-135).
 //
 // Layout in HBM (all per table, sized once for the worst-case batch):
-//   slots : uint2 {key, val}[capacity]   capacity = 1.25 x max_items by default (XG_TABLE_SLOTS_PCT): the
-//                                        worst-case batch of the headline config (8.45 M ids) gives an
-//                                        84 MB table that stays inside B200's 126 MB L2 while a batch
-//                                        is being sampled; 0xFFFFFFFF'FFFFFFFF = free
-//   n2o   : uint32[max_items]            local id -> global id  (the "unique" list, append only)
-//   items : uint32[kMaxFills + 1]        items[k] = number of unique ids after the k-th fill since
-//                                        Reset (items[0] = 0); lives on the device so that a whole
-//                                        minibatch can be enqueued without a host round trip.
+//   slots : uint32[capacity]   ONE 4-byte word per slot.  capacity = 1.5 x max_items by default
+//                              (XG_TABLE_SLOTS_PCT): the worst-case batch of the headline config (8.45 M ids) gives a
+//                              51 MB table.  The r01 table kept {key, val} pairs (8 bytes, 84 MB): measured on B200, a
+//                              randomly probed table stays L2-resident up to ~64 MB (fill cost per key doubles from
+//                              64 to 84 MB and triples at 256 MB, tools/table_size_probe.py) and every probe that
+//                              misses L2 is a DRAM row activation that the feature gather on the other stream pays
+//                              for.  0xFFFFFFFF = free.
+//   n2o   : uint32[max_items]  local id -> global id  (the "unique" list, append only)
+//   items : uint32[kMaxFills + 1]  items[k] = number of unique ids after the k-th fill since Reset (items[0] = 0);
+//                              lives on the device so that a whole minibatch can be enqueued without a host round trip.
 //
-// Determinism: while a fill is in flight `val` of a NEW key holds 0x80000000 | (smallest input
-// position that carries the key) -- maintained with atomicMin -- so the occurrence that numbers
-// the key is the FIRST in input order, not whichever CAS lands first as in the reference
-// (cuda_hashtable.cu:54-79).  Keys from earlier fills hold their local id (< 2^31), which atomicMin
-// against a tagged position can never change.
+// What a slot word means:
+//   0x80000000 | pos   (during a fill) the smallest input position of the CURRENT fill that carries the slot's key,
+//                      maintained with atomicMin - so the occurrence that numbers the key is the FIRST in input
+//                      order, not whichever CAS lands first as in the reference (cuda_hashtable.cu:54-79);
+//   local id < 2^31    (after the numbering pass, and for keys of earlier fills) - atomicMin against a tagged
+//                      position can never change it.
+// The KEY is not stored: it is keys[pos] of the current fill or n2o[local], both already in memory (and L2-resident:
+// 17 MB + 20 MB for the headline batch).  Only a probe that lands on an occupied slot has to look it up.
 #pragma once
 #include "common.cuh"
 
@@ -27,12 +32,12 @@ constexpr int kMaxFills = 62;
 constexpr uint32_t kPosTag = 0x80000000u;
 
 struct TableView {
-  uint2 *slots;
+  uint32_t *slots;
   uint32_t *n2o;
   uint32_t *n2o_slot;  // [max_items] slot position of every numbered key: lets Reset clear only those
   uint32_t *items;     // [kMaxFills + 1]
   uint32_t *overflow;  // set to 1 if capacity was exceeded
-  uint32_t cap;        // number of slots (any value, multiple of 2; not a power of two: sized to sit in L2)
+  uint32_t cap;        // number of slots (any value, multiple of 4; not a power of two: sized to sit in L2)
   uint32_t n2o_cap;
 };
 
@@ -42,17 +47,26 @@ __device__ __forceinline__ uint32_t table_hash(uint32_t k) {
   k ^= k >> 16; k *= 0x85EBCA6Bu; k ^= k >> 13; k *= 0xC2B2AE35u; k ^= k >> 16;
   return k;
 }
+__device__ __forceinline__ uint32_t table_home(const TableView &t, uint32_t key) {
+  return __umulhi(table_hash(key), t.cap);  // multiply-shift: any capacity, uses the hash's high bits
+}
 
-// Claim (or find) the slot of `key`; fold `tagged_pos` into its val with atomicMin.
-// Returns the slot position, or kEmpty if the table is full.
-__device__ __forceinline__ uint32_t table_insert(const TableView &t, uint32_t key, uint32_t tagged_pos) {
-  uint32_t p = __umulhi(table_hash(key), t.cap);  // multiply-shift: any capacity, uses the hash's high bits
+// key of an occupied slot.  `keys` = input array of the fill in flight (NULL outside a fill: every word is a local id).
+// Both arrays are read-only while the kernels that call this run, so plain loads are safe.
+__device__ __forceinline__ uint32_t table_key_of(const TableView &t, const uint32_t *__restrict__ keys, uint32_t word) {
+  if (word & kPosTag) return keys[word & ~kPosTag];
+  return word < t.n2o_cap ? t.n2o[word] : kEmpty;  // >= n2o_cap: the "numbered out of range" mark of an overflowed batch
+}
+
+// Claim (or find) the slot of keys[pos] and fold 0x80000000 | pos into it.  Returns the slot position, or kEmpty if the
+// table is full.  A free home slot - the common case - costs ONE atomic and nothing else.
+__device__ __forceinline__ uint32_t table_insert_resolve(const TableView &t, const uint32_t *__restrict__ keys,
+                                                         uint32_t key, uint32_t tagged_pos, uint32_t p, uint32_t old) {
   for (uint32_t probes = 0; probes < t.cap; ++probes) {
-    uint32_t *kp = &t.slots[p].x;
-    uint32_t k = *reinterpret_cast<volatile uint32_t *>(kp);
-    if (k == kEmpty) k = atomicCAS(kp, kEmpty, key);
-    if (k == kEmpty || k == key) {
-      atomicMin(&t.slots[p].y, tagged_pos);
+    if (probes) old = atomicCAS(&t.slots[p], kEmpty, tagged_pos);
+    if (old == kEmpty) return p;
+    if (table_key_of(t, keys, old) == key) {
+      if (old > tagged_pos) atomicMin(&t.slots[p], tagged_pos);  // only tagged words can be larger; fire and forget
       return p;
     }
     p = (p + 1 == t.cap) ? 0u : p + 1;
@@ -60,55 +74,20 @@ __device__ __forceinline__ uint32_t table_insert(const TableView &t, uint32_t ke
   *t.overflow = 1;
   return kEmpty;
 }
-
-// The same insert split in two so that a thread can have several home-slot operations in flight before it
-// resolves any of them (sample_uniform_kernel pipelines 4 edges per lane this way on the small, latency-bound
-// layers).  Here the home slot is claimed with ONE 64-bit CAS on the whole {key, val} word: a free slot takes the
-// key and the position in a single L2 round trip; only a key that is already there needs a second operation, a
-// fire-and-forget RED.min, skipped when the val that came back is already smaller (val only decreases during a
-// fill).  Measured on B200 (same box, papers100M shape): layers of 8 k / 128 k nodes 0.045 -> 0.037 ms and
-// 0.080 -> 0.075 ms; on the big layer (0.9 M nodes, bound by random-access throughput rather than latency) the
-// CAS-on-every-probe form is SLOWER than load-then-CAS (0.254 vs 0.229 ms), so table_insert above keeps that.
-constexpr unsigned long long kFreeSlot = ~0ull;
-__device__ __forceinline__ unsigned long long slot_word(uint32_t key, uint32_t val) {
-  return ((unsigned long long)val << 32) | key;  // uint2 {x = key, y = val}, little endian
-}
-__device__ __forceinline__ uint32_t table_insert_begin(const TableView &t, uint32_t key, uint32_t tagged_pos,
-                                                       unsigned long long *old_out) {
-  const uint32_t p = __umulhi(table_hash(key), t.cap);
-  *old_out = atomicCAS(reinterpret_cast<unsigned long long *>(&t.slots[p]), kFreeSlot, slot_word(key, tagged_pos));
-  return p;
-}
-__device__ __forceinline__ uint32_t table_insert_finish(const TableView &t, uint32_t key, uint32_t tagged_pos,
-                                                        uint32_t p, unsigned long long old) {
-  if (old == kFreeSlot) return p;
-  if ((uint32_t)old == key) {
-    if ((uint32_t)(old >> 32) > tagged_pos) atomicMin(&t.slots[p].y, tagged_pos);
-    return p;
-  }
-  // the home slot belongs to another key: linear probing from the next slot, looking before claiming
-  p = (p + 1 == t.cap) ? 0u : p + 1;
-  for (uint32_t probes = 1; probes < t.cap; ++probes) {
-    uint32_t *kp = &t.slots[p].x;
-    uint32_t k = *reinterpret_cast<volatile uint32_t *>(kp);
-    if (k == kEmpty) k = atomicCAS(kp, kEmpty, key);
-    if (k == kEmpty || k == key) {
-      atomicMin(&t.slots[p].y, tagged_pos);
-      return p;
-    }
-    p = (p + 1 == t.cap) ? 0u : p + 1;
-  }
-  *t.overflow = 1;
-  return kEmpty;
+__device__ __forceinline__ uint32_t table_insert(const TableView &t, const uint32_t *__restrict__ keys, uint32_t key,
+                                                 uint32_t tagged_pos) {
+  const uint32_t p = table_home(t, key);
+  const uint32_t old = atomicCAS(&t.slots[p], kEmpty, tagged_pos);
+  return table_insert_resolve(t, keys, key, tagged_pos, p, old);
 }
 
-// SearchO2N: slot position of `key`, kEmpty when absent.
+// SearchO2N: slot position of `key`, kEmpty when absent.  Outside a fill every occupied word is a local id.
 __device__ __forceinline__ uint32_t table_find(const TableView &t, uint32_t key) {
-  uint32_t p = __umulhi(table_hash(key), t.cap);
+  uint32_t p = table_home(t, key);
   for (uint32_t probes = 0; probes < t.cap; ++probes) {
-    uint32_t k = __ldg(&t.slots[p].x);
-    if (k == key) return p;
-    if (k == kEmpty) return kEmpty;
+    const uint32_t w = __ldg(&t.slots[p]);
+    if (w == kEmpty) return kEmpty;
+    if (w < t.n2o_cap && t.n2o[w] == key) return p;
     p = (p + 1 == t.cap) ? 0u : p + 1;
   }
   return kEmpty;
@@ -126,16 +105,20 @@ constexpr int kAssignBlock = 256;
 constexpr int kAssignItems = 4;
 constexpr int kAssignTile = kAssignBlock * kAssignItems;
 
-// insert keys[0..n) with positions 0..n-1; pos_out[i] = slot position. n from *d_n if d_n != NULL.
+// insert keys[0..n) with positions 0..n-1; pos_out[i] = slot position (must not alias keys). n from *d_n if d_n != NULL.
 int launch_table_insert(const TableView &t, const uint32_t *keys, uint32_t *pos_out, size_t n_max,
                         const uint64_t *d_n, cudaStream_t s);
-// number the first occurrences: items[fill] = items[fill-1] + #new; n2o appended; slot.val = local
-// local_out != NULL: also write local_out[i] = local id of the key at position i (the remap, fused: no second pass)
-int launch_table_assign(const TableView &t, const uint32_t *pos, size_t n_max, const uint64_t *d_n,
-                        int fill, const ScanSpace &scan, cudaStream_t s, uint32_t *local_out = nullptr);
+// number the first occurrences: items[fill] = items[fill-1] + #new; n2o appended; slot word = local id.  `keys` = the
+// array the positions were inserted from.
+// local_out != NULL (16-byte aligned): also write local_out[i] = local id of the key at position i (the remap, fused)
+// ids_into_table = false: the last fill before Reset - the ids are only handed out through local_out / n2o, the
+// slots keep their tagged positions (lookups after this fill are not possible)
+int launch_table_assign(const TableView &t, const uint32_t *keys, const uint32_t *pos, size_t n_max, const uint64_t *d_n,
+                        int fill, const ScanSpace &scan, cudaStream_t s, uint32_t *local_out = nullptr,
+                        bool ids_into_table = true);
 // Reset in O(items): slots[n2o_slot[i]] = free for i < items[fill], then items[] = 0 (stream-ordered)
 int launch_table_clear(const TableView &t, int fill, size_t max_items, cudaStream_t s);
-// out[i] = slots[pos[i]].val
+// out[i] = slots[pos[i]] (the local id, after the numbering pass)
 int launch_table_gather_local(const TableView &t, const uint32_t *pos, uint32_t *out, size_t n_max,
                               const uint64_t *d_n, cudaStream_t s);
 

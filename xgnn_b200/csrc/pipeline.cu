@@ -238,7 +238,7 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
   // FillWithDupRevised(output_nodes) (dist_loops.cc:106-107)
   XG_CUDA(cudaMemsetAsync(ln.scan_mem, 0, s->scan_bytes, st));
   if ((rc = launch_table_insert(t, b->seeds, ln.pos, B, d_nseed64, st))) return rc;
-  if ((rc = launch_table_assign(t, ln.pos, B, d_nseed64, 1, scan_b(s, ln), st, b->seed_local))) return rc;
+  if ((rc = launch_table_assign(t, b->seeds, ln.pos, B, d_nseed64, 1, scan_b(s, ln), st, b->seed_local))) return rc;
   mark();
 
   for (int l = L - 1; l >= 0; --l) {  // seeds outward (dist_loops.cc:120-123)
@@ -253,8 +253,6 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
     const uint32_t salt = kSampleSalt + (uint32_t)l;
     if (s->uniform) {
       SampleFusion fusion{};
-      fusion.table = t;
-      fusion.pos_out = ln.pos;
       fusion.src_local = src_local;
       fusion.csc_indptr = b->csc_indptr[l];
       fusion.enabled = true;
@@ -273,16 +271,17 @@ int enqueue_sample(xg_sampler *s, xg_batch *b) {
                                make_uint2(0, 0), &b->d_params->rng_key, salt, ln.ext, st);
       }
       if (rc) return rc;
-      // unfused: the neighbours go into the table in a pass of their own
-      if ((rc = launch_table_insert(t, ln.dst_global, ln.pos, s->cap_edge[l], d_num_edge, st))) return rc;
     }
     mark();
-    // FillWithDuplicates(out_dst) + GPUMapEdges (dist_loops.cc:279-297): number the new ids, then
-    // one 8-byte load per edge at the remembered slot gives the neighbour's local id
-    // ... and the neighbour's local id for every edge in the same pass (no second walk over the table)
-    if ((rc = launch_table_assign(t, ln.pos, s->cap_edge[l], d_num_edge, fill, scan_b(s, ln), st, b->row[l]))) return rc;
+    // the neighbours go into the table in a pass of their own (see SampleFusion): coalesced keys, one L2 atomic each
+    if ((rc = launch_table_insert(t, ln.dst_global, ln.pos, s->cap_edge[l], d_num_edge, st))) return rc;
     mark();
-    mark();  // (the separate remap stage of earlier revisions: fused above, kept as an empty stage for the timing ABI)
+    // FillWithDuplicates(out_dst) + GPUMapEdges (dist_loops.cc:279-297): number the new ids and, in the same pass,
+    // write the neighbour's local id for every edge (one 4-byte load per edge at the remembered slot)
+    if ((rc = launch_table_assign(t, ln.dst_global, ln.pos, s->cap_edge[l], d_num_edge, fill, scan_b(s, ln), st, b->row[l],
+                                  /*ids_into_table=*/l != 0)))  // layer 0 is the batch's last fill: nothing looks its ids up
+      return rc;
+    mark();
   }
 
   // task->input_nodes = the unique list (dist_loops.cc:357), already in place; counts leave the table before the next Reset
@@ -537,7 +536,7 @@ int xg_sampler_submit(xg_sampler *s, const uint32_t *seeds, size_t num_seeds, in
   }
   if (ln.dirty.exchange(false)) {  // after an overflow the targeted Reset cannot know every used slot
     const size_t cap = (size_t)ln.view.cap;
-    if (cudaMemsetAsync(ln.view.slots, 0xFF, cap * sizeof(uint2), st) != cudaSuccess ||
+    if (cudaMemsetAsync(ln.view.slots, 0xFF, cap * sizeof(uint32_t), st) != cudaSuccess ||
         cudaMemsetAsync(ln.view.items, 0, (kMaxFills + 2) * sizeof(uint32_t), st) != cudaSuccess) {
       b->claimed.store(0);
       return XG_ERR_CUDA;
@@ -683,7 +682,7 @@ int xg_batch_stage_ms(xg_batch *b, int stage, int layer, float *ms) {
   int first;  // index of the mark that opens the stage
   switch (stage) {
     case XG_STAGE_RESET_SEEDS: first = 0; break;
-    case XG_STAGE_SAMPLE: case XG_STAGE_NUMBER: case XG_STAGE_REMAP:
+    case XG_STAGE_SAMPLE: case XG_STAGE_INSERT: case XG_STAGE_NUMBER:
       XG_REQUIRE(layer >= 0 && layer < L, "layer out of range");
       first = 1 + 3 * (L - 1 - layer) + (stage - XG_STAGE_SAMPLE);
       break;

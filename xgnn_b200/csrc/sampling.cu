@@ -105,18 +105,16 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
     // ---------------- phase B: G lanes per node ---------------------------------------------
     if constexpr (VPL == 1 && PIPE) {
       // fanout <= G: a lane owns at most ONE edge of a node (slot gl).  The tile's nodes are walked kPipe at a
-      // time in three sweeps - positions + neighbour loads, stores + first hash probes, probe resolution - so
-      // every lane has kPipe independent DRAM loads and then kPipe independent L2 probes in flight instead of
-      // one dependent load -> probe -> CAS chain per node (that chain, 8-16 times per tile, was 70 % of the
-      // kernel: ncu r01b long-scoreboard stalls).  Same Philox counters and draws as before: outputs unchanged.
-      // Used for layers of at most one wave of tiles (seed-side layers: latency bound, 0.063 -> 0.046 ms and
-      // 0.088 -> 0.079 ms on B200); the big input-side layer is bound by random-sector DRAM throughput, where the
-      // extra registers (43 vs 32) only cost occupancy (0.26 -> 0.31 ms), so it keeps the plain loop.
+      // time in two sweeps - positions + neighbour loads, then the stores - so every lane has kPipe independent
+      // DRAM loads in flight instead of one dependent chain per node (that chain, 8-16 times per tile, was 70 % of
+      // the kernel: ncu r01b long-scoreboard stalls).  Same Philox counters and draws as the plain loop.
+      // Used for layers of at most one wave of tiles (seed-side layers: latency bound); the big input-side layer
+      // is bound by random-sector DRAM throughput, where extra registers only cost occupancy, so it keeps the
+      // plain loop.
       constexpr int kPipe = 4;
       static_assert((kSampleTile / kGroups) % kPipe == 0, "tile iterations must be a multiple of the pipeline depth");
       for (unsigned j0 = grp; j0 < kSampleTile; j0 += kGroups * kPipe) {
-        uint32_t nb[kPipe], slot[kPipe];
-        unsigned long long old0[kPipe];
+        uint32_t nb[kPipe];
         bool live[kPipe];
 #pragma unroll
         for (int q = 0; q < kPipe; ++q) {  // sweep 1: choose the position, issue the neighbour load
@@ -143,22 +141,12 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
           nb[q] = live[q] ? nedges[sel] : 0u;
         }
 #pragma unroll
-        for (int q = 0; q < kPipe; ++q) {  // sweep 2: write the edge, start the hash insert
+        for (int q = 0; q < kPipe; ++q) {  // sweep 2: write the edges
           if (!live[q]) continue;
           const unsigned j = j0 + q * kGroups;
           const uint64_t e = tile_base + s_off[j] + gl;
           out_dst[e] = nb[q];
           out_src[e] = s_src[j];
-          if (FUSED) slot[q] = table_insert_begin(fusion.table, nb[q], kPosTag | (uint32_t)e, &old0[q]);
-        }
-        if (FUSED) {
-#pragma unroll
-          for (int q = 0; q < kPipe; ++q) {  // sweep 3: resolve the probes
-            if (!live[q]) continue;
-            const unsigned j = j0 + q * kGroups;
-            const uint64_t e = tile_base + s_off[j] + gl;
-            fusion.pos_out[e] = table_insert_finish(fusion.table, nb[q], kPosTag | (uint32_t)e, slot[q], old0[q]);
-          }
         }
       }
     } else {
@@ -215,7 +203,6 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
               const uint64_t e = obase + s;
               out_dst[e] = nbr;
               out_src[e] = src;
-              if (FUSED) fusion.pos_out[e] = table_insert(fusion.table, nbr, kPosTag | (uint32_t)e);
             }
           }
         } else {
@@ -224,7 +211,6 @@ sample_uniform_kernel(const xg_graph g, const uint32_t *__restrict__ input, uint
             const uint64_t e = obase + s;
             out_dst[e] = nbr;
             out_src[e] = src;
-            if (FUSED) fusion.pos_out[e] = table_insert(fusion.table, nbr, kPosTag | (uint32_t)e);
           }
         }
       }

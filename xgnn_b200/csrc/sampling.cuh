@@ -8,14 +8,14 @@ namespace xg {
 constexpr int kSampleBlock = 256;       // threads per CTA
 constexpr int kSampleTile = 256;        // input nodes per tile (one per thread in the metadata phase)
 
-// Optional fusion of the remap work into the sampler (used by the minibatch pipeline):
+// Optional fusion of the src-side remap into the sampler (used by the minibatch pipeline):
 //   - out_src receives LOCAL ids (src_local[i], or i itself when src_local == NULL: the input list of
 //     every layer but the seed layer IS the unique list, so position == local id);
-//   - every sampled neighbour is inserted into the hash table with its final edge position, and the
-//     slot position is written to pos_out.
+//   - csc_indptr receives the block's CSC offsets.
+// (r01 also inserted every sampled neighbour into the hash table from inside the sampler.  With the 4-byte-slot table
+// a probe reads keys back through their edge positions, i.e. out_dst of OTHER threads of the same launch, which would
+// need a device-wide fence per edge; the insert is a kernel of its own again - one more coalesced pass over 17 MB.)
 struct SampleFusion {
-  TableView table;
-  uint32_t *pos_out;          // [num_input * fanout]
   const uint32_t *src_local;  // local id of input[i], or NULL for identity
   uint32_t *csc_indptr;       // [num_input + 1] or NULL: edge offset of every input node = the block's CSC indptr
   bool enabled;
