@@ -441,19 +441,20 @@ int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx,
     return e ? std::atoi(e) : 2;  // 2 = shared-memory ring (default), 0 / 1 = register-staged <16,4,4> / <16,8,2>
   }();
   if (vw == 16 && variant >= 2 && stats == nullptr) {
-    // shared-memory ring: XG_GATHER_RING_CTAS CTAs per SM (default 2), XG_GATHER_RING_STAGES x 2 KB per warp
-    // (default 3).  Measured on B200, papers100M-shape batch (profiles/r01d_sweep*.txt): alone 0.91-0.96 ms for
-    // every setting with >= 48 KB per SM in flight (register-staged kernel: 0.92-0.94); with the next batch's
-    // sample phase running beside it 1.42 ms/minibatch at (2 CTAs, 3 stages) vs 1.48 for the register-staged
-    // kernel and 1.56 with the two phases on one stream.
+    // shared-memory ring: XG_GATHER_RING_CTAS CTAs per SM (default 3), XG_GATHER_RING_STAGES x 2 KB per warp
+    // (default 4): 192 KB per SM in flight.  Measured on B200, papers100M-shape batch: alone the gather takes
+    // 0.84-0.96 ms for every setting with >= 48 KB per SM in flight (profiles/r01d_sweep*.txt), but with the next
+    // batch's sample phase running beside it - and, at N > 1, with a tenth to a fifth of the rows coming over NVLink
+    // at ~3x the latency - the deeper budget wins: r02, 1 GPU 1.190 -> 1.155 ms/minibatch, 2 GPUs 8.4 -> 8.9-9.0 G
+    // edges/s for (3 CTAs, 4 stages), (4, 3) and (2, 6) alike (all 192 KB) against (2, 3) = 96 KB.
     static const int ring_ctas = [] {
       const char *e = std::getenv("XG_GATHER_RING_CTAS");
-      const int v = e ? std::atoi(e) : 2;
+      const int v = e ? std::atoi(e) : 3;
       return v < 1 ? 1 : (v > 4 ? 4 : v);
     }();
     static const int ring_stages = [] {
       const char *e = std::getenv("XG_GATHER_RING_STAGES");
-      return e ? std::atoi(e) : 3;
+      return e ? std::atoi(e) : 4;
     }();
     int ring_dev = 0;
     XG_CUDA(cudaGetDevice(&ring_dev));
@@ -477,7 +478,7 @@ int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx,
       case 4: XG_RING(4); break;
       case 6: XG_RING(6); break;
       case 8: XG_RING(8); break;
-      default: XG_RING(3); break;
+      default: XG_RING(4); break;
     }
 #undef XG_RING
     XG_LAUNCHED();
