@@ -1,8 +1,8 @@
 #!/bin/bash
 # A/B harness: runs bench.py once per environment assignment given as arguments ("" = default) and prints ms/step + stages.
-# usage (on the GPU box): tools/ab.sh "" "XG_TABLE_PERSIST_MB=64" ...
+# usage (on the GPU box): tools/ab.sh "" "XG_TABLE_PERSIST_MB=64" ...   (XG_AB_ARGS = extra bench.py arguments)
 for cfg in "$@"; do
-  out=$(env $cfg python bench.py --steps 60 --warmup 10 --no-cpu-baseline --no-secondary --stage-steps 10 2>/dev/null | tail -1)
+  out=$(env $cfg python bench.py --steps 60 --warmup 10 --no-cpu-baseline --no-secondary --stage-steps 10 $XG_AB_ARGS 2>/dev/null | tail -1)
   python - "$cfg" <<PY
 import json,sys
 d=json.loads('''$out''')
