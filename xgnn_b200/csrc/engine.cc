@@ -1709,7 +1709,9 @@ void samgraph_report_epoch_average(uint64_t epoch) {
   samgraph_report_epoch(epoch);
   std::fflush(stdout);
 }
-void samgraph_report_node_access(void) {}  // SAMGRAPH_LOG_NODE_ACCESS statistics: not collected
+void samgraph_report_node_access(void) {  // Profiler::ReportNodeAccess (profiler.cc): SAMGRAPH_LOG_NODE_ACCESS statistics
+  std::fprintf(stderr, "[samgraph] node access statistics: not collected (SAMGRAPH_LOG_NODE_ACCESS is not implemented by xgnn_b200)\n");
+}
 
 // Chrome-trace style begin/end marks (profiler.cc TraceStepBegin/End, DumpTrace)
 namespace {

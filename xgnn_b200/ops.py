@@ -411,7 +411,7 @@ class MinibatchSampler:
         self._h = h
 
     def __del__(self):
-        if getattr(self, "_h", None):
+        if getattr(self, "_h", None) and lib is not None:  # `lib` is gone when the interpreter is shutting down
             lib.xg_sampler_destroy(self._h)
             self._h = None
 
