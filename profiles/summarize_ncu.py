@@ -19,7 +19,7 @@ def short(name: str) -> str:
     return name.strip()
 
 
-def launches(path: str, skip_prefixes=("synth_", "part_", "at::", "at_cuda_detail", "ncclDev")):
+def launches(path: str, skip_prefixes=("synth_", "part_", "at::", "at_cuda_detail", "ncclDev", "native::", "cuda::kernelHistogram", "cub::")):
     rows = [r for r in csv.reader(l for l in open(path) if l.startswith('"'))]
     hdr = rows[0]
     k, v = hdr.index("Kernel Name"), hdr.index("Metric Value")
