@@ -12,10 +12,18 @@
  *     against committed fixtures generated from it (tests/golden/*.npz).
  *   - hashtable properties: pinned against the reference's gtest vectors
  *     (samgraph/unittest/test_hashmap.cc:98-172).
- *   - khop0 deg > fanout, khop1/weighted/random-walk: distribution is the contract (the reference
- *     seeds from the wall clock / a default-seeded thread_local mt19937), so only the law is pinned.
- *   - routing / partition layout / miss-cache split: no reference test exists ("parity unpinned by
- *     the reference's tests"); restated from the cited lines.
+ *   - khop0 deg > fanout: distribution is the contract.  The repo kernel is tested against the uniform law and against
+ *     20 000 runs of the reference's CPU reservoir, whose inclusive RandomID(0, j + 1) law is derived and confirmed
+ *     (tests/test_ref_cuda.py::test_khop0_against_the_reference_cpu_reservoir).
+ *   - khop1 / weighted (alias, prefix, hash-dedup) / random-walk + top-K / khop3: the restatements below take the random
+ *     words as an input (GPU == oracle replay, bit for bit) AND the GPU kernels are pinned against the reference's own CUDA
+ *     kernels compiled in place (oracle/_ref/libxgnn_ref_cuda.so, tests/test_ref_cuda.py: exact where the draws do not
+ *     matter, two-sample chi-square elsewhere).
+ *   - presample ranking, ICS'22 placement (tests/oracle_lib.py restatement): pinned against the reference's own
+ *     PreSampler / ICS22SongPlacementSolver compiled in place (oracle/ref_host_shim.cc; goldens + live).
+ *   - mock extract (SAMGRAPH_EMPTY_FEAT): pinned against CPUMockExtract.
+ *   - routing / partition layout / miss-cache split: no reference test or CPU code exists ("parity unpinned by
+ *     the reference's tests"); restated from the cited lines and checked against feat[nodes] / the flat CSR.
  */
 #include <stdint.h>
 #include <stdlib.h>
