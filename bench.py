@@ -357,18 +357,21 @@ def exchange_parts(st, dist, torch):
     P, r = st.world, st.rank
     # the replica (two-tier store) and a replicated topology are private: never exported
     names = ["feat_part"] if st.local.get("replicate_topology") else ["indptr", "indices", "feat_part"]
-    mine, raw = [], {}
+    mine, raw = [], st.local.setdefault("raw", {})
     for nm in names:
         t = st.local[nm]
-        p = ctypes.c_void_p()
-        nbytes = t.numel() * t.element_size()
-        check(lib.xg_device_malloc(ctypes.byref(p), nbytes))
-        raw_t = torch.as_tensor(ops._DevMem(p.value, (nbytes,), "|u1", None), device="cuda")
-        raw_t.copy_(t.contiguous().view(torch.uint8).view(-1))
+        if nm in raw:  # generated straight into its own exportable block (build_store(exportable=True)): nothing to copy
+            p = ctypes.c_void_p(raw[nm])
+        else:
+            p = ctypes.c_void_p()
+            nbytes = t.numel() * t.element_size()
+            check(lib.xg_device_malloc(ctypes.byref(p), nbytes))
+            raw[nm] = p.value
+            raw_t = torch.as_tensor(ops._DevMem(p.value, (nbytes,), "|u1", None), device="cuda")
+            raw_t.copy_(t.contiguous().view(torch.uint8).view(-1))
         torch.cuda.synchronize()
         hnd = (ctypes.c_ubyte * 64)()
         check(lib.xg_ipc_export(p, hnd))
-        raw[nm] = p.value
         mine.append(bytes(hnd))
         st.local[nm] = None  # the torch copy is no longer needed
     torch.cuda.empty_cache()
@@ -387,7 +390,7 @@ def exchange_parts(st, dist, torch):
                 check(lib.xg_ipc_import((ctypes.c_ubyte * 64).from_buffer_copy(hb[64 * k:64 * k + 64]), ctypes.byref(out)))
                 ptrs[nm][q] = out.value
                 imported.append(out.value)
-    st.local["raw"], st.local["imported"] = raw, imported
+    st.local["imported"] = imported
     return ptrs
 
 
@@ -395,10 +398,13 @@ def release_store(R):
     """Give a run's memory back (secondary configs follow in the same process): peers first stop reading, then the
     IPC mappings are closed and the exported shards freed."""
     from xgnn_b200._clib import lib
-    torch, dist, st = R["torch"], R["dist"], R["st"]
+    import torch
+    dist, st = R.get("dist"), R.get("st")
     for k in ("sm", "topo", "graph"):
         R.pop(k, None)
     torch.cuda.synchronize()
+    if st is None:
+        return
     if dist is not None:
         dist.barrier()
     for p in st.local.get("imported", []):
@@ -416,7 +422,8 @@ def release_store(R):
     torch.cuda.empty_cache()
 
 
-def run_xgnn(args, dist=None):
+def run_xgnn(args, dist=None, R0=None):
+    """R0: dict filled as the run goes (store first), so that a failure half-way can still be cleaned up"""
     import torch
     from xgnn_b200 import dataset as D
     from xgnn_b200 import ops
@@ -432,7 +439,9 @@ def run_xgnn(args, dist=None):
                        replicate_pct=min(args.replicate, args.cache_pct),
                        replica_words=os.environ.get("XG_BENCH_REPLICA_WORDS", "1") != "0",
                        flat_when_full=os.environ.get("XG_BENCH_FORCE_TABLE", "0") == "0",  # 1: the N > 1 lookup path on one GPU
-                       replicate_topology=rep_topo)
+                       replicate_topology=rep_topo, exportable=world > 1)
+    if R0 is not None:
+        R0.update(st=st, dist=dist)
     ptrs = None
     if world > 1:
         ptrs = exchange_parts(st, dist, torch)
@@ -715,7 +724,15 @@ def epoch_pass(R, args, epochs=4):
 
 def one_config(args, dist, *, with_e2e=True, epochs=0):
     """build -> self-check -> timed run -> stage pass -> (epoch pass) -> release; returns the JSON fragment"""
-    R = run_xgnn(args, dist)
+    R = {}
+    try:
+        R.update(run_xgnn(args, dist, R))
+        return _one_config(R, args, with_e2e, epochs)
+    finally:  # also after a failure half-way (out of memory ...): the next config needs the memory back
+        release_store(R)
+
+
+def _one_config(R, args, with_e2e, epochs):
     st, world = R["st"], R["world"]
     stage_ms, info = stage_pass(R, args)
     roof, stages = summarize(R, args, stage_ms, info)
@@ -737,7 +754,6 @@ def one_config(args, dist, *, with_e2e=True, epochs=0):
         frag["epoch"].update(feature_gather_GBps=frag["feature_gather_GBps"], input_nodes_per_batch=info["rows"],
                              edges_per_batch=sum(info["edges"]))
     frag["_launches"], frag["_clocks"] = int(R["launches"]), R["clk"]
-    release_store(R)
     return frag
 
 
@@ -758,20 +774,21 @@ def secondary_configs(args, dist, world):
             ("cfg4 friendster / random walk top-K", dict(shape="friendster", scale=1, sample_type=3, cache_pct=1.0), False),
             ("cfg4 friendster / weighted KHop (alias)", dict(shape="friendster", scale=1, sample_type=2, cache_pct=1.0), False),
             ("cfg5 mag240M-homo / hot rows in HBM, cold rows in pinned host", dict(shape="mag240M-homo", scale=1, sample_type=0,
-                                                                                   cache_pct=0.2, steps=12, warmup=3, stage_steps=3), False),
+                                                                                   cache_pct=0.2, steps=12, warmup=3, stage_steps=3,
+                                                                                   in_flight=1), False),
         ]
     else:
         per_gpu_gb = 375.0 / world
-        full = min(1.0, 100.0 / per_gpu_gb)
+        full = min(1.0, 80.0 / per_gpu_gb)  # at most 80 GB of cached rows per GPU: batch slots (13 GB each) must fit beside them
         specs = [
             ("cfg3 twitter / KHop0, topology v % P over NVLink peers, features two-tier",
              dict(shape="twitter", scale=1, sample_type=0, cache_pct=1.0, replicate_topology=0), False),
             (f"cfg5 mag240M-homo / {full:.0%} of the rows sharded over the GPUs' HBM",
              dict(shape="mag240M-homo", scale=1, sample_type=0, cache_pct=full, replicate=0.0, replicate_topology=0, steps=12,
-                  warmup=3, stage_steps=3), False),
+                  warmup=3, stage_steps=3, in_flight=1), False),
             ("cfg5 mag240M-homo / half of that in HBM, cold rows in pinned host: HBM + NVLink + PCIe in one launch",
              dict(shape="mag240M-homo", scale=1, sample_type=0, cache_pct=full / 2, replicate=0.0, replicate_topology=0, steps=12,
-                  warmup=3, stage_steps=3), False),
+                  warmup=3, stage_steps=3, in_flight=1), False),
         ]
     out = []
     for name, kw, with_cpu in specs:

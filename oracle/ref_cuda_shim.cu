@@ -136,6 +136,10 @@ struct RefCudaGraph {
   // curand states live as long as the engine in the reference (dist/dist_engine.cc:431-433) and every kernel
   // stores them back, so batch k continues where batch k-1 stopped: one object per (sampler, fanout, batch size).
   std::map<std::tuple<int, size_t, size_t>, cuda::GPURandomStates *> states;
+  // optional GGMS partitioning of the same graph: DeviceDistGraph's pointer tables (cuda/dist_graph.h:114-151)
+  uint32_t num_part = 0, num_cache_node = 0;
+  uint32_t **d_part_indptr = nullptr, **d_part_indices = nullptr;
+  std::vector<uint32_t *> part_bufs;
 };
 
 }  // namespace
@@ -171,8 +175,34 @@ void refcu_graph_destroy(void *h) {
   cudaFree(g->prob);
   cudaFree(g->alias);
   cudaFree(g->prefix);
+  for (auto *b : g->part_bufs) cudaFree(b);
+  cudaFree(g->d_part_indptr);
+  cudaFree(g->d_part_indices);
   for (auto &kv : g->states) delete kv.second;
   delete g;
+}
+
+// Attach a GGMS partitioning of the graph: part p = CSR of the nodes v < num_cache_node with v % P == p (rebased, as
+// DistGraph::_DatasetPartition leaves it, dist_graph.cu:228-272); slot P = the whole CSR (pinned host memory in the
+// reference, the device copy here: the routing is the same).  After this call KHop0 / KHop3 / random walk run through
+// the reference's DeviceDistGraph instead of DeviceNormalGraph.
+void refcu_graph_set_parts(void *h, uint32_t num_part, uint32_t num_cache_node, const uint32_t *indptr_concat,
+                           const size_t *indptr_off, const uint32_t *indices_concat, const size_t *indices_off) {
+  auto *g = static_cast<RefCudaGraph *>(h);
+  SHIM_CUDA(cudaSetDevice(g->device));
+  std::vector<uint32_t *> ip(num_part + 1), ix(num_part + 1);
+  for (uint32_t p = 0; p < num_part; ++p) {
+    ip[p] = to_device(indptr_concat + indptr_off[p], indptr_off[p + 1] - indptr_off[p]);
+    ix[p] = to_device(indices_concat + indices_off[p], indices_off[p + 1] - indices_off[p]);
+    g->part_bufs.push_back(ip[p]);
+    g->part_bufs.push_back(ix[p]);
+  }
+  ip[num_part] = g->indptr;
+  ix[num_part] = g->indices;
+  g->d_part_indptr = to_device(ip.data(), ip.size());
+  g->d_part_indices = to_device(ix.data(), ix.size());
+  g->num_part = num_part;
+  g->num_cache_node = num_cache_node;
 }
 
 // Forget the curand states: the next call re-seeds from the wall clock like a fresh engine.
@@ -219,7 +249,19 @@ size_t refcu_sample(void *h, int sample_type, const uint32_t *input, size_t num_
   cuda::GPURandomStates &states = *g->states[key];
   StreamHandle stream = nullptr;
   cuda::DeviceNormalGraph graph(g->indptr, g->indices, g->num_node);
-
+  if (g->num_part > 0 && (sample_type == kKHop0 || sample_type == kKHop3 || sample_type == kRandomWalk)) {
+    cuda::DeviceDistGraph dgraph(g->d_part_indptr, g->d_part_indices, g->num_part, g->num_cache_node, g->num_node);
+    if (sample_type == kKHop0) {
+      cuda::GPUSampleKHop0(dgraph, d_input, num_input, fanout, d_src, d_dst, d_num_out, ctx, stream, &states, 0);
+    } else if (sample_type == kKHop3) {
+      cuda::GPUSampleKHop3(dgraph, d_input, num_input, fanout, d_src, d_dst, d_num_out, ctx, stream, &states, 0);
+    } else {
+      cuda::FrequencyHashmap fmap(num_input, num_random_walk * random_walk_length, ctx);
+      cuda::GPUSampleRandomWalk(dgraph, d_input, num_input, random_walk_length, restart_prob, num_random_walk, fanout,
+                                d_src, d_dst, d_data, d_num_out, &fmap, ctx, stream, &states, 0);
+      SHIM_CUDA(cudaDeviceSynchronize());
+    }
+  } else
   switch (sample_type) {
     case kKHop0:
       cuda::GPUSampleKHop0(graph, d_input, num_input, fanout, d_src, d_dst, d_num_out, ctx, stream,

@@ -509,6 +509,7 @@ if refcu is not None:
     _sig(refcu, "refcu_graph_create", c_void_p, c_int, u32p, u32p, c_uint32, c_size_t, c_void_p, c_void_p, c_void_p)
     _sig(refcu, "refcu_graph_destroy", None, c_void_p)
     _sig(refcu, "refcu_reset_states", None, c_void_p)
+    _sig(refcu, "refcu_graph_set_parts", None, c_void_p, c_uint32, c_uint32, u32p, c_void_p, u32p, c_void_p)
     _sig(refcu, "refcu_sample", c_size_t, c_void_p, c_int, u32p, c_size_t, c_size_t, c_size_t, c_double, c_size_t, u32p,
          u32p, u32p)
     _sig(refcu, "ref_ics22_solve", c_uint32, c_void_p, c_uint32, c_uint32, c_uint32, c_double, c_uint32, u32p, u32p, u32p,
@@ -556,6 +557,16 @@ class RefCudaGraph:
         if getattr(self, "h", None):
             refcu.refcu_graph_destroy(self.h)
             self.h = None
+
+    def set_parts(self, parts, num_cache_node):
+        """GGMS partitioning (list of (indptr, indices) per part, as partition_csr() returns them): KHop0 / KHop3 /
+        random walk then go through the reference's DeviceDistGraph (cuda/dist_graph.h:114-151)"""
+        ip = [u32(a) for a, _ in parts]
+        ix = [u32(b) if len(b) else np.zeros(1, np.uint32) for _, b in parts]
+        ipo = np.cumsum([0] + [len(a) for a in ip]).astype(np.uint64)
+        ixo = np.cumsum([0] + [len(b) for b in ix]).astype(np.uint64)
+        refcu.refcu_graph_set_parts(self.h, len(parts), num_cache_node, np.concatenate(ip), ipo.ctypes.data,
+                                    np.concatenate(ix), ixo.ctypes.data)
 
     def reset_states(self):
         """drop the curand states: the next call seeds fresh ones from the wall clock (cuda_random_states.cu:106-108)"""

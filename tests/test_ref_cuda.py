@@ -235,6 +235,33 @@ def test_reference_cold_start_correlation(gadget, capsys):
     assert p_cold < 1e-6 and p_warm > P_MIN and p_repo > P_MIN
 
 
+@pytest.mark.parametrize("P,ratio", [(2, 1.0), (3, 0.6), (8, 0.35)])
+def test_ggms_routing_equals_the_reference_device_dist_graph(P, ratio):
+    """DeviceDistGraph::_GetRealPartId / NumEdge / operator[] (cuda/dist_graph.h:114-151) - the reference's own class, over
+    partitions built by the oracle's partitioner - against the repo's route() over the same partitions: with fanout >=
+    every degree both samplers return whole neighbour lists, so the outputs must be EQUAL arrays (and equal to the flat
+    CSR's); node ids >= num_cache_node take the host slot in both."""
+    from xgnn_b200 import ops
+    nv, ne = 6000, 50000
+    indptr, indices = synth.make_graph(nv, ne, seed=31, max_deg=30)
+    fan = int(np.diff(indptr.astype(np.int64)).max())
+    ncn = O.num_cache_node(indptr, ratio)
+    parts = [O.partition_csr(indptr, indices, ncn, p, P) for p in range(P)]
+    rg = O.RefCudaGraph(indptr, indices)
+    inp = np.random.default_rng(P).permutation(nv)[:3000].astype(np.uint32)
+    flat_s, flat_d, _ = rg.sample(7, inp, fan)
+    rg.set_parts(parts, ncn)
+    keep = [(_dev(pi), _dev(px if len(px) else np.zeros(1, np.uint32))) for pi, px in parts]
+    gd = ops.make_graph(part_indptr=[k[0] for k in keep], part_indices=[k[1] for k in keep], num_cache_node=ncn,
+                        num_node=nv, host_indptr=_dev(indptr), host_indices=_dev(indices))
+    for st in (7, 0):
+        rs, rd, _ = rg.sample(st, inp, fan)
+        s, d = ops.GPUSampleKHop(gd, _dev(inp), fan, seed=1, batch_key=st, sample_type=st)
+        assert np.array_equal(rs, flat_s) and np.array_equal(rd, flat_d), "the reference's own routing changed its result"
+        assert np.array_equal(_u32(s), rs) and np.array_equal(_u32(d), rd)
+    assert (inp >= ncn).any() == (ratio < 1.0)
+
+
 # ---------------------------------------------------------------------------------------------- random walk + top-K
 def _walk_sets(src, dst, cnt):
     return sorted(zip(src.tolist(), dst.tolist(), cnt.tolist()))

@@ -64,8 +64,9 @@ def gen_csr(begin: int, stride: int, n: int, num_node: int, c: float, seed: int,
     return indptr, indices, num_edge
 
 
-def gen_features(n_rows: int, dim: int, dtype, device, *, row_ids=None, begin: int = 0, stride: int = 1):
-    out = torch.empty((n_rows, dim), dtype=dtype, device=device)
+def gen_features(n_rows: int, dim: int, dtype, device, *, row_ids=None, begin: int = 0, stride: int = 1, out=None):
+    if out is None:
+        out = torch.empty((n_rows, dim), dtype=dtype, device=device)
     code = 0 if dtype == torch.float32 else 2
     check(lib.xg_synth_features(out.data_ptr(), None if row_ids is None else row_ids.data_ptr(), begin, stride,
                                 n_rows, dim, code, _stream()))
@@ -110,14 +111,17 @@ def cache_rank_nodes(num_node: int, num_cached: int, num_replicated: int = 0) ->
 def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale: int = 1, cache_pct: float = 1.0,
                 replicate_pct: float = 0.0, with_features: bool = True, seed: int = SYNTH_SEED,
                 flat_when_full: bool = True, replica_words: bool = True, replicate_topology: bool = False,
-                empty_feat: int = 20) -> GGMSStore:
+                empty_feat: int = 20, exportable: bool = False) -> GGMSStore:
     """Generate THIS rank's shards (topology part `rank`, feature part `rank`) of the named shape,
     scaled down by `scale`. Peer parts are attached afterwards (attach_peers) from IPC handles.
     replicate_topology: every GPU keeps the whole CSR (B200 option: papers100M's 6.9 GB fits everywhere, so the sample
     phase needs no NVLink; the reference's `v % P` sharding stays the default and is what config 3 asks for).
     cache_pct < 1: the uncached rows live in pinned host memory; the host tier is a SAMGRAPH_EMPTY_FEAT-style mock table
     of 2^empty_feat rows (node v reads row v & mask, cuda/cuda_extraction.cu:51-72), as the reference's evaluation
-    scripts run shapes whose feature file does not fit - the PCIe traffic is real, the host footprint small."""
+    scripts run shapes whose feature file does not fit - the PCIe traffic is real, the host footprint small.
+    exportable: the feature shard is generated straight into an xg_device_malloc block (its own cudaMalloc, 2 MiB granular:
+    what a CUDA IPC handle can name, dist_graph.cu:274-307) instead of torch's pool, so that sharing it needs no second copy
+    of a shard that may fill half the GPU; the raw pointer is kept in st.local["raw"]."""
     V, E, dim, dtype, num_class, train_frac = SHAPES[shape]
     V, E = V // scale, E // scale
     dev = torch.device("cuda", device)
@@ -153,7 +157,16 @@ def build_store(shape: str, device: int, rank: int = 0, world: int = 1, *, scale
             table[ranks] = np.arange(n_cached, dtype=np.uint32)
             st.local["cache_table"] = torch.from_numpy(table.view(np.int32)).to(dev)
             mine = torch.from_numpy(np.ascontiguousarray(ranks[n_rep:][rank::P]).view(np.int32)).to(dev)
-            st.local["feat_part"] = gen_features(max(mine.numel(), 1), dim, dtype, dev, row_ids=mine if mine.numel() else None)
+            part_out = None
+            if exportable:
+                import ctypes
+                raw = ctypes.c_void_p()
+                rows = max(mine.numel(), 1)
+                check(lib.xg_device_malloc(ctypes.byref(raw), rows * st.row_bytes))
+                st.local.setdefault("raw", {})["feat_part"] = raw.value
+                part_out = torch.as_tensor(ops._DevMem(raw.value, (rows, dim), ops._TYPESTR[dtype], None), device=dev)
+            st.local["feat_part"] = gen_features(max(mine.numel(), 1), dim, dtype, dev, row_ids=mine if mine.numel() else None,
+                                                 out=part_out)
             st.local["num_cached"] = n_cached
             st.local["num_replicated"] = n_rep
             if n_cached < V:  # cold tier: pinned host memory, read over PCIe through UVA
