@@ -27,6 +27,7 @@
 
 #include "common/common.h"
 #include "common/constant.h"
+#include "common/cuda/cuda_cache_manager.h"
 #include "common/cuda/cuda_frequency_hashmap.h"
 #include "common/cuda/cuda_function.h"
 #include "common/cuda/cuda_random_states.h"
@@ -322,6 +323,69 @@ size_t refcu_sample(void *h, int sample_type, const uint32_t *input, size_t num_
   cudaFree(d_data);
   cudaFree(d_num_out);
   return num_out;
+}
+
+// ---------------------------------------------------------------------------------------------
+// The reference's single-GPU feature cache: GPUCacheManager (cuda/cuda_cache_manager_host.cc:62-131 builds the
+// direct-address table and the cached rows; cuda_cache_manager_device.cu:355-441 GetMissCacheIndex, :573-625
+// GPUExtractMissData, :656-731 CombineCacheData).  Both files are compiled in place; this only feeds them.
+struct RefCache {
+  cuda::GPUCacheManager *mgr = nullptr;
+  void *mem = nullptr;        // zeroed storage of the object: its first constructor leaves _dist_graph unset
+  void *host_feat = nullptr;  // pinned copy of the feature table: extract_miss_data loads it from the GPU (UVA)
+  int device = 0;
+  size_t row_bytes = 0;
+};
+
+void *refcu_cache_create(int device, const void *feat, size_t num_node, size_t dim, int dtype, size_t elem_bytes,
+                         const uint32_t *rank_nodes, double cache_percentage) {
+  SHIM_CUDA(cudaSetDevice(device));
+  auto *c = new RefCache();
+  c->device = device;
+  c->row_bytes = dim * elem_bytes;
+  SHIM_CUDA(cudaHostAlloc(&c->host_feat, num_node * c->row_bytes, cudaHostAllocMapped));
+  memcpy(c->host_feat, feat, num_node * c->row_bytes);
+  if (RunConfig::omp_thread_num <= 0) RunConfig::omp_thread_num = 4;
+  RunConfig::option_empty_feat = 0;
+  c->mem = calloc(1, sizeof(cuda::GPUCacheManager));
+  c->mgr = new (c->mem) cuda::GPUCacheManager(GPU(device), GPU(device), c->host_feat, static_cast<DataType>(dtype), dim,
+                                              rank_nodes, num_node, cache_percentage);
+  SHIM_CUDA(cudaDeviceSynchronize());
+  return c;
+}
+
+void refcu_cache_destroy(void *h) {
+  auto *c = static_cast<RefCache *>(h);
+  c->mgr->~GPUCacheManager();
+  free(c->mem);
+  cudaFreeHost(c->host_feat);
+  delete c;
+}
+
+// DoArch6GetCacheMissIndex + DoArch6GPUCacheFeatureCopy for one node list (dist/dist_loops.cc:1015-1074, 1209-1285): the
+// split, then miss rows from the host table and cached rows from the cache into out_feat[n x row_bytes].
+void refcu_cache_extract(void *h, const uint32_t *nodes, size_t n, void *out_feat, uint32_t *miss_src,
+                         uint32_t *miss_dst, size_t *num_miss, uint32_t *cache_src, uint32_t *cache_dst,
+                         size_t *num_cache) {
+  auto *c = static_cast<RefCache *>(h);
+  SHIM_CUDA(cudaSetDevice(c->device));
+  uint32_t *d_nodes = to_device(nodes, n), *d_idx = nullptr;
+  void *d_out = nullptr;
+  SHIM_CUDA(cudaMalloc(&d_idx, (n ? n : 1) * 4 * sizeof(uint32_t)));
+  SHIM_CUDA(cudaMalloc(&d_out, (n ? n : 1) * c->row_bytes));
+  uint32_t *d_ms = d_idx, *d_md = d_idx + n, *d_cs = d_idx + 2 * n, *d_cd = d_idx + 3 * n;
+  c->mgr->GetMissCacheIndex(d_ms, d_md, num_miss, d_cs, d_cd, num_cache, d_nodes, n, nullptr);
+  c->mgr->GPUExtractMissData(d_out, d_ms, d_md, *num_miss, nullptr);
+  c->mgr->CombineCacheData(d_out, d_cs, d_cd, *num_cache, nullptr);
+  SHIM_CUDA(cudaDeviceSynchronize());
+  SHIM_CUDA(cudaMemcpy(out_feat, d_out, n * c->row_bytes, cudaMemcpyDeviceToHost));
+  SHIM_CUDA(cudaMemcpy(miss_src, d_ms, *num_miss * 4, cudaMemcpyDeviceToHost));
+  SHIM_CUDA(cudaMemcpy(miss_dst, d_md, *num_miss * 4, cudaMemcpyDeviceToHost));
+  SHIM_CUDA(cudaMemcpy(cache_src, d_cs, *num_cache * 4, cudaMemcpyDeviceToHost));
+  SHIM_CUDA(cudaMemcpy(cache_dst, d_cd, *num_cache * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_nodes);
+  cudaFree(d_idx);
+  cudaFree(d_out);
 }
 
 }  // extern "C"

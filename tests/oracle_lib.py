@@ -509,6 +509,10 @@ if refcu is not None:
     _sig(refcu, "refcu_graph_create", c_void_p, c_int, u32p, u32p, c_uint32, c_size_t, c_void_p, c_void_p, c_void_p)
     _sig(refcu, "refcu_graph_destroy", None, c_void_p)
     _sig(refcu, "refcu_reset_states", None, c_void_p)
+    _sig(refcu, "refcu_cache_create", c_void_p, c_int, c_void_p, c_size_t, c_size_t, c_int, c_size_t, u32p, c_double)
+    _sig(refcu, "refcu_cache_destroy", None, c_void_p)
+    _sig(refcu, "refcu_cache_extract", None, c_void_p, u32p, c_size_t, c_void_p, u32p, u32p, POINTER(c_size_t), u32p, u32p,
+         POINTER(c_size_t))
     _sig(refcu, "refcu_graph_set_parts", None, c_void_p, c_uint32, c_uint32, u32p, c_void_p, u32p, c_void_p)
     _sig(refcu, "refcu_sample", c_size_t, c_void_p, c_int, u32p, c_size_t, c_size_t, c_size_t, c_double, c_size_t, u32p,
          u32p, u32p)
@@ -580,3 +584,30 @@ class RefCudaGraph:
         n = refcu.refcu_sample(self.h, sample_type, inp, len(inp), fanout, walk_length, restart_prob, num_walk, src,
                                dst, data)
         return src[:n].copy(), dst[:n].copy(), data[:n].copy()
+
+
+class RefCudaCache:
+    """The reference's GPUCacheManager (single-GPU feature cache) built from (feat, rank list, cache percentage)"""
+
+    def __init__(self, feat, rank_nodes, cache_percentage, device=0):
+        feat = np.ascontiguousarray(feat)
+        self.feat, self.ranks = feat, u32(rank_nodes)
+        code = REF_DTYPE[feat.dtype] if ref is not None else {np.dtype(np.float32): 0, np.dtype(np.float16): 2}[feat.dtype]
+        self.h = refcu.refcu_cache_create(device, feat.ctypes.data, feat.shape[0], feat.shape[1], code, feat.itemsize,
+                                          self.ranks, cache_percentage)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            refcu.refcu_cache_destroy(self.h)
+            self.h = None
+
+    def extract(self, nodes):
+        """-> (rows, miss_src, miss_dst, cache_src, cache_dst) of GetMissCacheIndex + GPUExtractMissData + CombineCacheData"""
+        nodes = u32(nodes)
+        n = len(nodes)
+        out = np.empty((n, self.feat.shape[1]), self.feat.dtype)
+        idx = [np.empty(max(n, 1), np.uint32) for _ in range(4)]
+        nm, nc = c_size_t(0), c_size_t(0)
+        refcu.refcu_cache_extract(self.h, nodes, n, out.ctypes.data, idx[0], idx[1], ctypes.byref(nm), idx[2], idx[3],
+                                  ctypes.byref(nc))
+        return out, idx[0][:nm.value].copy(), idx[1][:nm.value].copy(), idx[2][:nc.value].copy(), idx[3][:nc.value].copy()

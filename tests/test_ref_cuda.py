@@ -262,6 +262,40 @@ def test_ggms_routing_equals_the_reference_device_dist_graph(P, ratio):
     assert (inp >= ncn).any() == (ratio < 1.0)
 
 
+@pytest.mark.parametrize("dtype,dim,pct", [(np.float32, 128, 0.3), (np.float16, 768, 0.6), (np.float32, 100, 1.0), (np.float32, 64, 0.0)])
+def test_feature_cache_path_equals_the_reference_cache_manager(dtype, dim, pct):
+    """The reference's own GPUCacheManager - its constructor builds the direct-address table and the cached rows
+    (cuda_cache_manager_host.cc:62-131), GetMissCacheIndex splits a node list (cuda_cache_manager_device.cu:355-441),
+    GPUExtractMissData + CombineCacheData fill the rows (:573-731) - against the repo's operators on the same inputs:
+    the four index lists equal element for element, the rows equal byte for byte, in the three-call form and in the
+    single fused launch."""
+    import torch
+    from xgnn_b200 import ops
+    nv = 30000
+    feat = synth.make_features(nv, dim, dtype)
+    indptr, _ = synth.make_graph(nv, 200000, seed=8)
+    rank = synth.degree_rank(indptr)
+    rc = O.RefCudaCache(feat, rank, pct)
+    # a minibatch's input nodes are unique (the reference CHECKs num_cache <= num_cached_nodes on that assumption)
+    nodes = np.random.default_rng(dim).permutation(nv)[:20001].astype(np.uint32)
+    want, ms, md, cs, cd = rc.extract(nodes)
+    assert want.tobytes() == feat[nodes].tobytes(), "the reference's own path must return feat[nodes]"
+    ncached = int(nv * pct)
+    table = O.build_cache_table(rank, ncached, nv)
+    cache_rows = feat[rank[:ncached]] if ncached else np.zeros((1, dim), dtype)
+    h_feat = torch.from_numpy(feat).pin_memory()
+    store = ops.make_feature_store(feat.strides[0], h_feat, _dev(table), [torch.from_numpy(cache_rows).cuda()], local_parts=(0,))
+    gms, gmd, gcs, gcd = ops.GetMissCacheIndex(_dev(table), _dev(nodes))
+    assert np.array_equal(_u32(gms), ms) and np.array_equal(_u32(gmd), md)
+    assert np.array_equal(_u32(gcs), cs) and np.array_equal(_u32(gcd), cd)
+    out = ops.ExtractGGMS(store, _dev(nodes), dim, h_feat.dtype)
+    assert out.cpu().numpy().tobytes() == want.tobytes()
+    out2 = torch.empty_like(out)
+    ops.GPUExtractMissData(out2, h_feat, gms, gmd, feat.strides[0])
+    ops.CombineCacheData(out2, store, gcs, gcd)
+    assert out2.cpu().numpy().tobytes() == want.tobytes()
+
+
 # ---------------------------------------------------------------------------------------------- random walk + top-K
 def _walk_sets(src, dst, cnt):
     return sorted(zip(src.tolist(), dst.tolist(), cnt.tolist()))
