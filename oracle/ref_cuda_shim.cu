@@ -30,6 +30,7 @@
 #include "common/cuda/cuda_cache_manager.h"
 #include "common/cuda/cuda_frequency_hashmap.h"
 #include "common/cuda/cuda_function.h"
+#include "common/cuda/cuda_hashtable.h"
 #include "common/cuda/cuda_random_states.h"
 #include "common/cuda/dist_graph.h"
 #include "common/device.h"
@@ -386,6 +387,71 @@ void refcu_cache_extract(void *h, const uint32_t *nodes, size_t n, void *out_fea
   cudaFree(d_nodes);
   cudaFree(d_idx);
   cudaFree(d_out);
+}
+
+// ---------------------------------------------------------------------------------------------
+// The reference's GPU OrderedHashTable (cuda/cuda_hashtable.cu:699-1064) and GPUMapEdges (cuda/cuda_mapping.cu:50-80).
+// Among duplicate occurrences of one id its winner is whichever CAS lands first (cuda_hashtable.cu:54-79), so tests
+// compare sets / prefix / round trips there and exact arrays where the input of a fill has no duplicates.
+struct RefTable {
+  cuda::OrderedHashTable *t = nullptr;
+  int device = 0;
+};
+
+void *refcu_table_create(int device, size_t size) {
+  SHIM_CUDA(cudaSetDevice(device));
+  auto *r = new RefTable();
+  r->device = device;
+  r->t = new cuda::OrderedHashTable(size, GPU(device), nullptr);
+  SHIM_CUDA(cudaDeviceSynchronize());
+  return r;
+}
+void refcu_table_destroy(void *h) {
+  auto *r = static_cast<RefTable *>(h);
+  delete r->t;
+  delete r;
+}
+void refcu_table_reset(void *h) { static_cast<RefTable *>(h)->t->Reset(nullptr); }
+size_t refcu_table_num_items(void *h) { return static_cast<RefTable *>(h)->t->NumItems(); }
+
+// FillWithDuplicates (unique_kind 0) or FillWithUnique (1); unique_out (host, capacity >= NumItems after the fill)
+// receives the whole unique list.
+size_t refcu_table_fill(void *h, int unique_kind, const uint32_t *input, size_t n, uint32_t *unique_out, size_t cap) {
+  auto *r = static_cast<RefTable *>(h);
+  SHIM_CUDA(cudaSetDevice(r->device));
+  uint32_t *d_in = to_device(input, n), *d_unique = nullptr;
+  SHIM_CUDA(cudaMalloc(&d_unique, (cap ? cap : 1) * 4));
+  IdType num_unique = 0;
+  if (unique_kind == 1) {
+    r->t->FillWithUnique(d_in, n, nullptr);
+    num_unique = r->t->NumItems();
+    r->t->CopyUnique(d_unique, nullptr);
+  } else {
+    r->t->FillWithDuplicates(d_in, n, d_unique, &num_unique, nullptr);
+  }
+  SHIM_CUDA(cudaDeviceSynchronize());
+  if (num_unique > cap) abort();
+  SHIM_CUDA(cudaMemcpy(unique_out, d_unique, (size_t)num_unique * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_in);
+  cudaFree(d_unique);
+  return num_unique;
+}
+
+void refcu_table_map_edges(void *h, const uint32_t *src, const uint32_t *dst, size_t n, uint32_t *new_src,
+                           uint32_t *new_dst) {
+  auto *r = static_cast<RefTable *>(h);
+  SHIM_CUDA(cudaSetDevice(r->device));
+  uint32_t *d_src = to_device(src, n), *d_dst = to_device(dst, n), *d_ns = nullptr, *d_nd = nullptr;
+  SHIM_CUDA(cudaMalloc(&d_ns, (n ? n : 1) * 4));
+  SHIM_CUDA(cudaMalloc(&d_nd, (n ? n : 1) * 4));
+  cuda::GPUMapEdges(d_src, d_ns, d_dst, d_nd, n, r->t->DeviceHandle(), GPU(r->device), nullptr);
+  SHIM_CUDA(cudaDeviceSynchronize());
+  SHIM_CUDA(cudaMemcpy(new_src, d_ns, n * 4, cudaMemcpyDeviceToHost));
+  SHIM_CUDA(cudaMemcpy(new_dst, d_nd, n * 4, cudaMemcpyDeviceToHost));
+  cudaFree(d_src);
+  cudaFree(d_dst);
+  cudaFree(d_ns);
+  cudaFree(d_nd);
 }
 
 }  // extern "C"

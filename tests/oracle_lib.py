@@ -509,6 +509,12 @@ if refcu is not None:
     _sig(refcu, "refcu_graph_create", c_void_p, c_int, u32p, u32p, c_uint32, c_size_t, c_void_p, c_void_p, c_void_p)
     _sig(refcu, "refcu_graph_destroy", None, c_void_p)
     _sig(refcu, "refcu_reset_states", None, c_void_p)
+    _sig(refcu, "refcu_table_create", c_void_p, c_int, c_size_t)
+    _sig(refcu, "refcu_table_destroy", None, c_void_p)
+    _sig(refcu, "refcu_table_reset", None, c_void_p)
+    _sig(refcu, "refcu_table_num_items", c_size_t, c_void_p)
+    _sig(refcu, "refcu_table_fill", c_size_t, c_void_p, c_int, u32p, c_size_t, u32p, c_size_t)
+    _sig(refcu, "refcu_table_map_edges", None, c_void_p, u32p, u32p, c_size_t, u32p, u32p)
     _sig(refcu, "refcu_cache_create", c_void_p, c_int, c_void_p, c_size_t, c_size_t, c_int, c_size_t, u32p, c_double)
     _sig(refcu, "refcu_cache_destroy", None, c_void_p)
     _sig(refcu, "refcu_cache_extract", None, c_void_p, u32p, c_size_t, c_void_p, u32p, u32p, POINTER(c_size_t), u32p, u32p,
@@ -611,3 +617,32 @@ class RefCudaCache:
         refcu.refcu_cache_extract(self.h, nodes, n, out.ctypes.data, idx[0], idx[1], ctypes.byref(nm), idx[2], idx[3],
                                   ctypes.byref(nc))
         return out, idx[0][:nm.value].copy(), idx[1][:nm.value].copy(), idx[2][:nc.value].copy(), idx[3][:nc.value].copy()
+
+
+class RefCudaTable:
+    """The reference's GPU OrderedHashTable (cuda/cuda_hashtable.cu) + GPUMapEdges (cuda/cuda_mapping.cu)"""
+
+    def __init__(self, size, device=0):
+        self.size = size
+        self.h = refcu.refcu_table_create(device, size)
+
+    def __del__(self):
+        if getattr(self, "h", None):
+            refcu.refcu_table_destroy(self.h)
+            self.h = None
+
+    def reset(self):
+        refcu.refcu_table_reset(self.h)
+
+    def fill(self, ids, unique_input=False):
+        """FillWithDuplicates (or FillWithUnique) -> the whole unique list afterwards"""
+        ids = u32(ids)
+        out = np.empty(self.size, np.uint32)
+        n = refcu.refcu_table_fill(self.h, 1 if unique_input else 0, ids, len(ids), out, self.size)
+        return out[:n].copy()
+
+    def map_edges(self, src, dst):
+        src, dst = u32(src), u32(dst)
+        ns, nd = np.empty(max(len(src), 1), np.uint32), np.empty(max(len(src), 1), np.uint32)
+        refcu.refcu_table_map_edges(self.h, src, dst, len(src), ns, nd)
+        return ns[:len(src)].copy(), nd[:len(src)].copy()

@@ -296,6 +296,49 @@ def test_feature_cache_path_equals_the_reference_cache_manager(dtype, dim, pct):
     assert out2.cpu().numpy().tobytes() == want.tobytes()
 
 
+def test_hashtable_against_the_reference_gpu_table():
+    """cuda::OrderedHashTable + GPUMapEdges, the reference's own (cuda_hashtable.cu:699-1064, cuda_mapping.cu:50-80).
+    Its winner among duplicate occurrences is whichever CAS lands first, so: EXACT equality of the unique list and of
+    the remapped edges wherever a fill's input has no duplicates (FillWithUnique, and FillWithDuplicates of fresh
+    ids: the reference's numbering is then the input order, i.e. ours); with duplicates: equal sets, equal counts,
+    the reference's earlier list is a prefix of its later one exactly as ours is of ours, and both remaps invert to
+    the same global ids."""
+    from xgnn_b200 import ops
+    rng = np.random.default_rng(11)
+    space, cap = 200000, 60000
+    seeds = rng.permutation(space)[:5000].astype(np.uint32)
+    fresh = np.setdiff1d(rng.permutation(space)[:20000].astype(np.uint32), seeds)[:9000]
+    rng.shuffle(fresh)
+    dup = rng.integers(0, space, size=30000).astype(np.uint32)
+    rt, t = O.RefCudaTable(cap), ops.OrderedHashTable(cap)
+    t.Reset()
+    # fill 1: unique seeds -> identical lists
+    u_ref = rt.fill(seeds, unique_input=True)
+    t.FillWithUnique(_dev(seeds))
+    assert np.array_equal(u_ref, seeds) and np.array_equal(_u32(t.RefUnique()), seeds)
+    # fill 2: duplicate-free fresh ids through the duplicate-tolerant path -> still identical, seeds stay the prefix
+    u_ref = rt.fill(fresh)
+    u_own = _u32(t.FillWithDuplicates(_dev(fresh)))
+    assert np.array_equal(u_ref, u_own) and np.array_equal(u_own[:len(seeds)], seeds)
+    rs, rd = rt.map_edges(seeds[:4000], fresh[:4000])
+    s, d = ops.GPUMapEdges(_dev(seeds[:4000]), _dev(fresh[:4000]), t)
+    assert np.array_equal(_u32(s), rs) and np.array_equal(_u32(d), rd)
+    # fill 3: heavy duplication -> order inside the NEW part may differ (the reference is racy), everything else may not
+    before = len(u_own)
+    u_ref = rt.fill(dup)
+    u_own = _u32(t.FillWithDuplicates(_dev(dup)))
+    assert len(u_ref) == len(u_own) and np.array_equal(u_ref[:before], u_own[:before])
+    assert np.array_equal(np.sort(u_ref[before:]), np.sort(u_own[before:]))
+    assert len(np.unique(u_ref)) == len(u_ref)
+    rs, rd = rt.map_edges(dup[::-1].copy(), dup)
+    s, d = ops.GPUMapEdges(_dev(dup[::-1].copy()), _dev(dup), t)
+    assert np.array_equal(u_ref[rd], dup) and np.array_equal(u_own[_u32(d)], dup)
+    assert np.array_equal(u_ref[rs], dup[::-1]) and np.array_equal(u_own[_u32(s)], dup[::-1])
+    # ours is the deterministic legal outcome: first occurrence order (CPUHashTable0)
+    first = dup[np.sort(np.unique(dup, return_index=True)[1])]
+    assert np.array_equal(u_own[before:], first[~np.isin(first, u_own[:before])])
+
+
 # ---------------------------------------------------------------------------------------------- random walk + top-K
 def _walk_sets(src, dst, cnt):
     return sorted(zip(src.tolist(), dst.tolist(), cnt.tolist()))
