@@ -402,6 +402,9 @@ def release_store(R):
     dist, st = R.get("dist"), R.get("st")
     for k in ("sm", "topo", "graph"):
         R.pop(k, None)
+    c = R.pop("clocks", None)
+    if c is not None and c.proc is not None and c.proc.poll() is None:  # a failed run: do not leave nvidia-smi behind
+        c.stop()
     torch.cuda.synchronize()
     if st is None:
         return
@@ -422,7 +425,7 @@ def release_store(R):
     torch.cuda.empty_cache()
 
 
-def run_xgnn(args, dist=None, R0=None):
+def run_xgnn(args, dist=None, R0=None, keep_clocks=False):
     """R0: dict filled as the run goes (store first), so that a failure half-way can still be cleaned up"""
     import torch
     from xgnn_b200 import dataset as D
@@ -539,7 +542,7 @@ def run_xgnn(args, dist=None, R0=None):
     e2e_edges, _ = run(args.warmup, args.steps, h_flat)
     barrier()
     e2e_s = time.perf_counter() - t0
-    clk = clocks.stop()
+    clk = None if keep_clocks else clocks.stop()  # the epoch pass that follows is part of the measurement: keep sampling
 
     def allmax(x):
         if dist is None:
@@ -559,7 +562,7 @@ def run_xgnn(args, dist=None, R0=None):
     edges_all, e2e_edges_all, rows_all = allsum(edges), allsum(e2e_edges), allsum(rows)
     return dict(torch=torch, dist=dist, rank=rank, world=world, local=local, st=st, sm=sm, ms=ms_max, e2e_s=e2e_max,
                 edges=edges_all, e2e_edges=e2e_edges_all, rows=rows_all, my_edges=edges, my_rows=rows,
-                launches=launches, clk=clk, num_edge=num_edge, t_build=t_build, batches=batches, d_flat=d_flat,
+                launches=launches, clk=clk, clocks=clocks, num_edge=num_edge, t_build=t_build, batches=batches, d_flat=d_flat,
                 offs=offs, stream=stream, self_check=oks, allmax=allmax, allsum=allsum, barrier=barrier, graph=graph,
                 weights=weights, topo=topo)
 
@@ -726,7 +729,7 @@ def one_config(args, dist, *, with_e2e=True, epochs=0):
     """build -> self-check -> timed run -> stage pass -> (epoch pass) -> release; returns the JSON fragment"""
     R = {}
     try:
-        R.update(run_xgnn(args, dist, R))
+        R.update(run_xgnn(args, dist, R, keep_clocks=epochs > 0))
         return _one_config(R, args, with_e2e, epochs)
     finally:  # also after a failure half-way (out of memory ...): the next config needs the memory back
         release_store(R)
@@ -751,6 +754,7 @@ def _one_config(R, args, with_e2e, epochs):
                        "note": f"host seeds -> xg_sampler_submit (H2D inside) -> xg_batch_wait (D2H counts); {args.in_flight} batches in flight"}
     if epochs:
         frag["epoch"] = epoch_pass(R, args, epochs)
+        R["clk"] = R["clocks"].stop()  # nvidia-smi sampled every 100 ms from the timed steps through the measured epochs
         frag["epoch"].update(feature_gather_GBps=frag["feature_gather_GBps"], input_nodes_per_batch=info["rows"],
                              edges_per_batch=sum(info["edges"]))
     frag["_launches"], frag["_clocks"] = int(R["launches"]), R["clk"]

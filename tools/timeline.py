@@ -20,12 +20,14 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--scale", type=int, default=1)
 ap.add_argument("--in-flight", type=int, default=2)
 ap.add_argument("--steps", type=int, default=24)
+ap.add_argument("--no-extract", action="store_true", help="sample phase alone (no feature store, no labels): what the captured graph costs without the gather beside it")
 a = ap.parse_args()
 torch.cuda.set_device(0)
 st = D.attach(D.build_store("papers100M", 0, 0, 1, scale=a.scale))
 stream = torch.cuda.Stream(priority=-1)
-sm = ops.MinibatchSampler(st.graph, bench.FANOUT, 8000, store=st.store, feat_dim=st.dim, feat_dtype=st.dtype,
-                          label=st.label, seed=2024, num_slots=a.in_flight + 1, device=0, stream=stream)
+sm = ops.MinibatchSampler(st.graph, bench.FANOUT, 8000, store=None if a.no_extract else st.store, feat_dim=st.dim,
+                          feat_dtype=st.dtype, label=None if a.no_extract else st.label, seed=2024, num_slots=a.in_flight + 1,
+                          device=0, stream=stream)
 batches = bench.seed_batches(st.train, 0, 1, 8000, a.steps)
 d = [torch.from_numpy(b.view(np.int32)).cuda() for b in batches]
 pend, rows = [], []
