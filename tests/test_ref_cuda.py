@@ -182,20 +182,25 @@ def _simulate_runs_hist(gd, st, d, fanout, n):
     return np.bincount(runs, minlength=fanout + 1)[:fanout + 1]
 
 
-@pytest.mark.parametrize("st,fanout,reps", [(7, 5, 6), (7, 10, 4), (6, 5, 6), (6, 10, 4), (7, 39, 2), (0, 5, 1), (0, 16, 1)])
+@pytest.mark.parametrize("st,fanout,reps", [(7, 5, 6), (7, 10, 4), (6, 5, 6), (6, 10, 4), (7, 39, 2), (0, 5, 1), (0, 16, 1), (5, 5, 6),
+                                            (5, 10, 4)])
 def test_without_replacement_samplers_match_reference_kernels(gadget, st, fanout, reps):
-    """KHop3 (cuda_sampling_khop3.cu:78-146), weighted hash-dedup (weighted_khop_hash_dedup.cu:59-116): exact for
+    """KHop3 (cuda_sampling_khop3.cu:78-146), KHop2 (cuda_sampling_khop2.cu), weighted hash-dedup
+    (weighted_khop_hash_dedup.cu:59-116): exact for
     degree <= fanout, two-sample chi-square on per-edge inclusion otherwise.  KHop0's GPU kernel re-seeds every launch
     with curand_init(thread + num_input) and applies its lane-parallel replacements in racy order
     (cuda_sampling_khop0.cu:114-117): only its exact part is compared here; its law is covered by
     test_khop0_against_the_reference_cpu_reservoir."""
     inp = gadget["hubs"]
+    # KHop2 (cuda_sampling_khop2.cu:46-375) shuffles the lists of the nodes it samples IN PLACE: it gets a graph copy of
+    # its own, so that the order it leaves behind cannot reach the other samplers (or another fanout) through the fixture
+    rg = O.RefCudaGraph(gadget["indptr"], gadget["indices"]) if st == 5 else gadget["rg"]
     tabs = []
     for who in ("ref", "repo"):
         t = np.zeros((len(DEGS), max(DEGS)), np.int64)
         for r in range(reps):
             if who == "ref":
-                s, d, _ = _ref_sample(gadget["rg"], st, inp, fanout)
+                s, d, _ = _ref_sample(rg, st, inp, fanout)
             else:
                 s, d = _repo_sample(gadget, st, inp, fanout, key=r)
             _check_structure(gadget, st, s, d, inp, fanout)
