@@ -215,6 +215,18 @@ int xg_get_miss_cache_index(const uint32_t *d_cache_table, const uint32_t *d_nod
                             uint32_t *d_miss_src, uint32_t *d_miss_dst, size_t *h_num_miss,
                             uint32_t *d_cache_src, uint32_t *d_cache_dst, size_t *h_num_cache,
                             void *stream);
+/* xg_get_miss_cache_index for callers that cannot allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid cudaMalloc.
+ * Same split, same output arrays (num_nodes entries each); the two counts go to caller memory on the DEVICE
+ * (d_counts[0] = misses, d_counts[1] = cache hits) and the call neither synchronises nor allocates: its scan scratch is
+ * a file-scope __device__ array of XG_NOALLOC_MAX_NODES / 1024 + 4 words of 8 bytes (128 KB) that every GPU loading
+ * the library holds until exit.  num_nodes > XG_NOALLOC_MAX_NODES -> XG_ERR_INVALID (xg_last_error says so).
+ * All calls on one device share that array: calls that overlap on the GPU (different streams without an ordering
+ * between them) race; calls on one stream, or ordered by events, are safe. */
+#define XG_NOALLOC_MAX_NODES (1u << 24)
+int xg_get_miss_cache_index_noalloc(const uint32_t *d_cache_table, const uint32_t *d_nodes, size_t num_nodes,
+                                    uint32_t *d_miss_src, uint32_t *d_miss_dst, uint32_t *d_cache_src,
+                                    uint32_t *d_cache_dst, uint64_t *d_counts, void *stream);
 /* GPUMockExtract (cuda/cuda_extraction.cu:118-160; CPU twin cpu/cpu_extraction.cc:47-64): dst[i] = src[index[i] & (2^k - 1)],
  * the SAMGRAPH_EMPTY_FEAT=k mock-feature mode of the reference's evaluation scripts; k = 0 is plain GPUExtract */
 int xg_mock_extract(void *d_dst, const void *src, const uint32_t *d_index, size_t num_index, size_t row_bytes,

@@ -148,6 +148,7 @@ _sig("xg_extract", c_int, c_void_p, c_void_p, _u32p, c_size_t, c_size_t, c_int, 
 _sig("xg_extract_ggms", c_int, POINTER(XgFeatureStore), _u32p, c_size_t, c_void_p, c_void_p, c_void_p)
 _sig("xg_get_miss_cache_index", c_int, _u32p, _u32p, c_size_t, _u32p, _u32p, POINTER(c_size_t), _u32p, _u32p,
      POINTER(c_size_t), c_void_p)
+_sig("xg_get_miss_cache_index_noalloc", c_int, _u32p, _u32p, c_size_t, _u32p, _u32p, _u32p, _u32p, c_void_p, c_void_p)
 _sig("xg_mock_extract", c_int, c_void_p, c_void_p, _u32p, c_size_t, c_size_t, c_uint32, c_void_p)
 _sig("xg_extract_miss_data", c_int, c_void_p, c_void_p, _u32p, _u32p, c_size_t, c_size_t, c_void_p)
 _sig("xg_combine_cache_data", c_int, c_void_p, POINTER(XgFeatureStore), _u32p, _u32p, c_size_t, c_void_p)

@@ -18,6 +18,7 @@
 #include <cub/cub.cuh>
 
 #include <cstdlib>
+#include <mutex>
 
 namespace xg {
 
@@ -765,5 +766,67 @@ extern "C" int xg_build_replica_words(const uint32_t *d_cache_table, uint32_t nu
   XG_CUDA(e);
   XG_REQUIRE(h_mismatch[0] == 0, "the replicated tier is not laid out by node id (cache_table[v] != rank of v among replicated nodes)");
   if (h_cover_all) *h_cover_all = h_mismatch[1] == 0 ? 1u : 0u;
+  return XG_OK;
+}
+
+// ---- GetMissCacheIndex without any allocation ------------------------------------------------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+// it).  The scan scratch of split_miss_cache_kernel - one ticket word plus one look-back word per tile - lives in a
+// file-scope __device__ array: every GPU that loads the library holds XG_NOALLOC_MAX_NODES / 1024 + 4 words of 8 bytes
+// (128 KB) until exit.  ALL calls on a device share it and it keeps the last call's contents, so the part a call uses
+// is cleared on the caller's stream first; two calls that overlap on the GPU (different streams, no ordering) race.
+namespace xg {
+namespace {
+
+constexpr size_t kStaticSplitTiles = (size_t)XG_NOALLOC_MAX_NODES / kSplitTile + 1;
+static __device__ __align__(256) uint64_t g_static_split_scratch[kStaticSplitTiles + 3];  // [0] ticket, [1..2] unused, [3..] scan
+
+constexpr int kStaticSplitDevices = 64;
+std::mutex g_static_split_mu;
+uint64_t *g_static_split_ptr[kStaticSplitDevices];  // device address of the array, per device (host code cannot use its name)
+
+// once per device, with that device current: the symbol's device address
+int static_split_scratch(uint64_t **out) {
+  int dev = 0;
+  XG_CUDA(cudaGetDevice(&dev));
+  XG_REQUIRE(dev >= 0 && dev < kStaticSplitDevices, "device ordinal beyond the static scratch table");
+  std::lock_guard<std::mutex> lock(g_static_split_mu);
+  if (!g_static_split_ptr[dev]) {
+    void *p = nullptr;
+    XG_CUDA(cudaGetSymbolAddress(&p, g_static_split_scratch));
+    XG_REQUIRE(p != nullptr, "cudaGetSymbolAddress returned NULL for the static split scratch");
+    g_static_split_ptr[dev] = static_cast<uint64_t *>(p);
+  }
+  *out = g_static_split_ptr[dev];
+  return XG_OK;
+}
+
+}  // namespace
+}  // namespace xg
+
+extern "C" int xg_get_miss_cache_index_noalloc(const uint32_t *d_cache_table, const uint32_t *d_nodes, size_t num_nodes,
+                                               uint32_t *d_miss_src, uint32_t *d_miss_dst, uint32_t *d_cache_src,
+                                               uint32_t *d_cache_dst, uint64_t *d_counts, void *stream) {
+  XG_REQUIRE(d_cache_table && d_counts, "NULL argument");
+  if (num_nodes > (size_t)XG_NOALLOC_MAX_NODES) {
+    set_error("invalid argument: xg_get_miss_cache_index_noalloc: num_nodes = " + std::to_string(num_nodes) +
+              " exceeds XG_NOALLOC_MAX_NODES = " + std::to_string((size_t)XG_NOALLOC_MAX_NODES) +
+              " (the static scratch is sized for that; use xg_get_miss_cache_index)");
+    return XG_ERR_INVALID;
+  }
+  XG_REQUIRE(num_nodes == 0 || (d_nodes && d_miss_src && d_miss_dst && d_cache_src && d_cache_dst), "NULL argument");
+  cudaStream_t s = as_stream(stream);
+  if (num_nodes == 0) {
+    XG_CUDA(cudaMemsetAsync(d_counts, 0, 2 * sizeof(uint64_t), s));
+    return XG_OK;
+  }
+  uint64_t *words = nullptr;
+  if (int rc = static_split_scratch(&words)) return rc;
+  const size_t tiles = (num_nodes + kSplitTile - 1) / kSplitTile + 1;
+  XG_CUDA(cudaMemsetAsync(words, 0, (tiles + 3) * sizeof(uint64_t), s));  // ticket + this call's scan words start at zero
+  split_miss_cache_kernel<<<grid_for(tiles, 8), kSplitBlock, 0, s>>>(
+      d_cache_table, d_nodes, num_nodes, d_miss_src, d_miss_dst, d_cache_src, d_cache_dst,
+      reinterpret_cast<unsigned long long *>(d_counts), reinterpret_cast<uint32_t *>(words), words + 3);
+  XG_LAUNCHED();
   return XG_OK;
 }
