@@ -33,6 +33,7 @@
 #include "common/cuda/cuda_hashtable.h"
 #include "common/cuda/cuda_random_states.h"
 #include "common/cuda/dist_graph.h"
+#include "common/cuda/ics22_song_dist_feature.h"
 #include "common/device.h"
 #include "common/logging.h"
 #include "common/profiler.h"
@@ -145,6 +146,20 @@ struct RefCudaGraph {
 };
 
 }  // namespace
+
+// The one thing the partitioned feature cache adds to CombineCacheData is WHERE a cache rank lives: the reference's
+// combine_cache_data_for_partition<T, Feat> (cuda_cache_manager_device.cu:277-299, file-local) reads
+// Feat::Get<T>(rank, col).  This kernel calls the reference's own device accessors - DeviceDistFeature::Get
+// (cuda/dist_graph.h:193-207: part rank % P, row rank / P) and DeviceICS22SongDistFeature::Get
+// (cuda/ics22_song_dist_feature.h:27-47: owner in the top bits, or the device_map / new_idx_map pair) - for every
+// (rank, column); the parts are laid out by the caller exactly as DistGraph::FeatureLoad leaves them
+// (dist_graph.cu:492-505: part p holds cache_rank_node[p], [p + P], ... in that order).
+template <typename T, typename Feat>
+__global__ void shim_dist_feature_rows(Feat feat, const samgraph::common::IdType *ranks, size_t n, uint32_t dim, T *out) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n * dim; i += (size_t)gridDim.x * blockDim.x) {
+    out[i] = feat.template Get<T>(ranks[i / dim], (samgraph::common::IdType)(i % dim));
+  }
+}
 
 extern "C" {
 
@@ -452,6 +467,46 @@ void refcu_table_map_edges(void *h, const uint32_t *src, const uint32_t *dst, si
   cudaFree(d_dst);
   cudaFree(d_ns);
   cudaFree(d_nd);
+}
+
+
+// rows (float32, dim columns) of `ranks` through the reference's partitioned-feature accessors.
+//   compact_bitwidth == 0 and device_map == NULL: DeviceDistFeature over num_part parts
+//   compact_bitwidth != 0: DeviceICS22SongDistFeature, compact ids;  device_map != NULL: its two-map form
+// parts_concat / part_off (in ELEMENTS): part p = parts_concat[part_off[p] .. part_off[p + 1])
+void refcu_dist_feature_get(int device, const float *parts_concat, const size_t *part_off, uint32_t num_part,
+                            uint32_t num_cache_node, uint32_t dim, uint32_t compact_bitwidth,
+                            const uint32_t *device_map, const uint32_t *new_idx_map, uint32_t num_map,
+                            const uint32_t *ranks, size_t n, float *out) {
+  SHIM_CUDA(cudaSetDevice(device));
+  std::vector<void *> parts(num_part);
+  for (uint32_t p = 0; p < num_part; ++p) parts[p] = to_device(parts_concat + part_off[p], part_off[p + 1] - part_off[p]);
+  void **d_parts = to_device(parts.data(), parts.size());
+  IdType *d_ranks = to_device(ranks, n), *d_dev = nullptr, *d_idx = nullptr;
+  float *d_out = nullptr;
+  SHIM_CUDA(cudaMalloc(&d_out, (n * dim ? n * dim : 1) * sizeof(float)));
+  if (n) {
+    if (compact_bitwidth == 0 && device_map == nullptr) {
+      cuda::DeviceDistFeature feat(d_parts, num_part, num_cache_node, dim);
+      shim_dist_feature_rows<float><<<296, 256>>>(feat, d_ranks, n, dim, d_out);
+    } else {
+      if (device_map) {
+        d_dev = to_device(device_map, num_map);
+        d_idx = to_device(new_idx_map, num_map);
+      }
+      cuda::DeviceICS22SongDistFeature feat(d_parts, d_dev, d_idx, num_cache_node, dim, compact_bitwidth);
+      shim_dist_feature_rows<float><<<296, 256>>>(feat, d_ranks, n, dim, d_out);
+    }
+    SHIM_CUDA(cudaGetLastError());
+  }
+  SHIM_CUDA(cudaDeviceSynchronize());
+  SHIM_CUDA(cudaMemcpy(out, d_out, n * dim * sizeof(float), cudaMemcpyDeviceToHost));
+  for (void *p : parts) cudaFree(p);
+  cudaFree(d_parts);
+  cudaFree(d_ranks);
+  cudaFree(d_dev);
+  cudaFree(d_idx);
+  cudaFree(d_out);
 }
 
 }  // extern "C"

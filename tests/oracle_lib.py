@@ -525,6 +525,27 @@ if refcu is not None:
     _sig(refcu, "ref_ics22_solve", c_uint32, c_void_p, c_uint32, c_uint32, c_uint32, c_double, c_uint32, u32p, u32p, u32p,
          u32p)
     _sig(refcu, "ref_presample_rank", None, c_uint32, c_int, c_size_t, u32p, c_void_p, u32p, u32p)
+    _sig(refcu, "refcu_dist_feature_get", None, c_int, f32p, c_void_p, c_uint32, c_uint32, c_uint32, c_uint32, c_void_p,
+         c_void_p, c_uint32, u32p, c_size_t, f32p)
+
+
+def ref_dist_feature_get(parts, num_cache_node, ranks, compact_bitwidth=0, device_map=None, new_idx_map=None, device=0):
+    """rows of `ranks` through the REFERENCE's device accessors: DeviceDistFeature::Get (cuda/dist_graph.h:193-207) over
+    the float32 parts, or DeviceICS22SongDistFeature::Get (cuda/ics22_song_dist_feature.h:27-47) when compact_bitwidth
+    or the (device_map, new_idx_map) pair is given"""
+    dim = parts[0].shape[1]
+    flat = [np.ascontiguousarray(p, np.float32).ravel() for p in parts]
+    off = np.zeros(len(parts) + 1, np.uint64)
+    np.cumsum([len(f) for f in flat], out=off[1:])
+    cat = np.concatenate(flat + [np.zeros(1, np.float32)])
+    ranks = u32(ranks)
+    out = np.empty((len(ranks), dim), np.float32)
+    dm = u32(device_map) if device_map is not None else None
+    im = u32(new_idx_map) if new_idx_map is not None else None
+    refcu.refcu_dist_feature_get(device, cat, off.ctypes.data, len(parts), num_cache_node, dim, compact_bitwidth,
+                                 dm.ctypes.data if dm is not None else None, im.ctypes.data if im is not None else None,
+                                 len(dm) if dm is not None else 0, ranks, len(ranks), out.reshape(-1))
+    return out
 
 
 def ref_ics22_solve(weight, num_cached, num_dev, clique_size, alpha):

@@ -1,7 +1,8 @@
 """The repo's sampler kernels against the REFERENCE's own CUDA samplers, both running on this GPU.
 
-oracle/_ref/libxgnn_ref_cuda.so = the reference's cuda_sampling_khop{0,1,3}.cu, cuda_sampling_weighted_khop*.cu,
-cuda_sampling_random_walk.cu, cuda_frequency_hashmap.cu and cuda_random_states.cu compiled in place for sm_100
+oracle/_ref/libxgnn_ref_cuda.so = the reference's cuda_sampling_khop{0,1,2,3}.cu, cuda_sampling_weighted_khop*.cu,
+cuda_sampling_random_walk.cu, cuda_frequency_hashmap.cu, cuda_random_states.cu, cuda_cache_manager_*.cu, cuda_hashtable.cu
+and the device accessors of dist_graph.h / ics22_song_dist_feature.h compiled in place for sm_100
 (oracle/Makefile `refcuda`, oracle/ref_cuda_shim.cu).  These are the only files that define KHop1 / weighted /
 random-walk behaviour (the CPU twins are empty stubs), so this is where SURVEY 8a rows a5, a6, a7 are pinned:
 
@@ -299,6 +300,79 @@ def test_feature_cache_path_equals_the_reference_cache_manager(dtype, dim, pct):
     ops.GPUExtractMissData(out2, h_feat, gms, gmd, feat.strides[0])
     ops.CombineCacheData(out2, store, gcs, gcd)
     assert out2.cpu().numpy().tobytes() == want.tobytes()
+
+
+@pytest.mark.parametrize("P,pct,dim", [(1, 0.5, 16), (2, 0.3, 128), (3, 1.0, 25), (8, 0.6, 100)])
+def test_partitioned_cache_routing_equals_the_reference_device_dist_feature(P, pct, dim):
+    """SURVEY 8a row a14: where a cache rank lives.  The reference's own DeviceDistFeature::Get (cuda/dist_graph.h:193-207;
+    what combine_cache_data_for_partition reads, cuda_cache_manager_device.cu:277-299) run on this GPU over parts laid out
+    as DistGraph::FeatureLoad leaves them (dist_graph.cu:492-505), against the repo's CombineCacheData and fused gather over
+    the same parts: byte for byte, and both equal feat[rank_node[rank]]."""
+    import torch
+    from xgnn_b200 import ops
+    nv = 20011
+    feat = synth.make_features(nv, dim)
+    indptr, _ = synth.make_graph(nv, 150000, seed=6)
+    rank = synth.degree_rank(indptr)
+    ncached = int(nv * pct)
+    parts = [O.partition_features(feat, rank, ncached, p, P) for p in range(P)]
+    rng = np.random.default_rng(P)
+    ranks = rng.permutation(ncached)[: min(ncached, 9001)].astype(np.uint32)
+    want = O.ref_dist_feature_get(parts, ncached, ranks)
+    assert want.tobytes() == feat[rank[ranks]].tobytes(), "the reference accessor over FeatureLoad's layout returns the ranked node's row"
+    table = O.build_cache_table(rank, ncached, nv)
+    h_feat = torch.from_numpy(feat).pin_memory()
+    d_parts = [torch.from_numpy(p).cuda() if len(p) else torch.zeros((1, dim), device="cuda") for p in parts]
+    d_table = _dev(table)  # the store keeps raw pointers: the tensors must outlive it
+    store = ops.make_feature_store(dim * 4, h_feat, d_table, d_parts, local_parts=(0,))
+    out = torch.full((len(ranks), dim), -1.0, device="cuda")
+    dst = np.arange(len(ranks), dtype=np.uint32)
+    ops.CombineCacheData(out, store, _dev(ranks), _dev(dst))
+    assert out.cpu().numpy().tobytes() == want.tobytes()
+    # by node id through the table (the fused launch): cached nodes resolve to the same (part, row) the reference reads
+    nodes = rank[ranks]
+    got = ops.ExtractGGMS(store, _dev(nodes), dim, torch.float32)
+    assert got.cpu().numpy().tobytes() == want.tobytes()
+
+
+@pytest.mark.parametrize("num_dev,clique,alpha,pct", [(4, 4, 0.0, 0.1), (4, 2, 0.5, 0.2), (8, 8, 0.2, 0.05)])
+def test_ics22_compact_routing_equals_the_reference_device_accessor(num_dev, clique, alpha, pct):
+    """DeviceICS22SongDistFeature::Get (cuda/ics22_song_dist_feature.h:27-47), the reference's own, in both of its forms -
+    the (device_map, new_idx_map) pair and the compact `owner << (32 - bitwidth) | row` ids - over the placement the
+    reference's own solver produced (ref_ics22_solve, compiled in place): the repo's gather through the compact table reads
+    the same rows, for every worker's view."""
+    import ctypes
+    import torch
+    from xgnn_b200 import ops
+    from xgnn_b200._clib import check, lib
+    V, E, dim, bw = 6000, 90000, 24, 3
+    indptr, indices = synth.make_graph(V, E, seed=11, max_deg=400)
+    feat = synth.make_features(V, dim)
+    weight = np.bincount(indices, minlength=V).astype(np.float64)
+    n_cached = int(V * pct)
+    ranking, dev_map, idx_map, cached, total = O.ref_ics22_solve(weight, n_cached, num_dev, clique, alpha)
+    parts_np = [feat[cached[d]] for d in range(num_dev)]  # ICS22SongDistGraph::FeatureLoad: CPUExtract of the slot list
+    h_nodes, h_w = O.ics22_in_degree_rank(indices, V)
+    d_parts = [torch.from_numpy(p).cuda() for p in parts_np]
+    host = torch.from_numpy(feat).cuda()
+    rng = np.random.default_rng(2)
+    for w in range(num_dev):
+        table, slots, tot = np.empty(V, np.uint32), np.empty(n_cached, np.uint32), ctypes.c_uint32(0)
+        check(lib.xg_ics22_placement(h_nodes.ctypes.data, h_w.ctypes.data, V, n_cached, num_dev, clique, alpha, w, bw,
+                                     table.ctypes.data, slots.ctypes.data, ctypes.addressof(tot)))
+        reachable = np.nonzero(dev_map[w] != 0xFFFFFFFF)[0].astype(np.uint32)
+        assert np.array_equal(np.nonzero(table != 0xFFFFFFFF)[0], reachable)
+        nodes = rng.permutation(reachable)[:3000].astype(np.uint32)
+        by_maps = O.ref_dist_feature_get(parts_np, V, nodes, device_map=dev_map[w], new_idx_map=idx_map[w])
+        by_compact = O.ref_dist_feature_get(parts_np, V, table[nodes], compact_bitwidth=bw)
+        assert by_maps.tobytes() == feat[nodes].tobytes() == by_compact.tobytes()
+        d_table = _dev(table)
+        st = ops.make_feature_store(dim * 4, host, d_table, parts=d_parts, local_parts=(w,), compact_bitwidth=bw)
+        got = ops.ExtractGGMS(st, _dev(nodes), dim, torch.float32)
+        assert got.cpu().numpy().tobytes() == by_compact.tobytes()
+        out = torch.full((len(nodes), dim), -1.0, device="cuda")
+        ops.CombineCacheData(out, st, _dev(table[nodes]), _dev(np.arange(len(nodes), dtype=np.uint32)))
+        assert out.cpu().numpy().tobytes() == by_compact.tobytes()
 
 
 def test_hashtable_against_the_reference_gpu_table():

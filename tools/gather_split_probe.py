@@ -35,6 +35,28 @@ for b in range(3):
     order = torch.argsort(peer.to(torch.int8), stable=True)
     variants = {"mixed": nodes, "split": nodes[order].contiguous()}
     out = torch.empty((nodes.numel(), st.dim), dtype=st.dtype, device="cuda")
+    # "concurrent": the two classes as two launches on two streams AT THE SAME TIME (rank + destination lists per class)
+    pos = torch.arange(nodes.numel(), device="cuda", dtype=torch.int32)
+    lists = [(r[m].to(torch.int32).contiguous(), pos[m].contiguous()) for m in (~peer, peer)]
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    ts = []
+    for it in range(6):
+        dist.barrier(); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for sx, (src, dst) in zip(streams, lists):
+            sx.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(sx):
+                ops.CombineCacheData(out, st.store, src, dst)
+        for sx in streams:
+            torch.cuda.current_stream().wait_stream(sx)
+        e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    res.setdefault("concurrent", []).append(min(ts[1:]))
+    want = torch.empty_like(out)
+    ops.ExtractGGMS(st.store, nodes, st.dim, st.dtype, out=want)
+    assert torch.equal(out.view(torch.int32), want.view(torch.int32)), "concurrent two-class gather differs from the mixed one"
     for name, nd in variants.items():
         ts = []
         for it in range(6):
@@ -45,8 +67,9 @@ for b in range(3):
             ts.append(e0.elapsed_time(e1))
         res.setdefault(name, []).append(min(ts[1:]))
     res.setdefault("peer_frac", []).append(float(peer.float().mean()))
-t = torch.tensor([np.mean(res["mixed"]), np.mean(res["split"])], device="cuda", dtype=torch.float64)
+t = torch.tensor([np.mean(res["mixed"]), np.mean(res["split"]), np.mean(res["concurrent"])], device="cuda", dtype=torch.float64)
 dist.all_reduce(t, op=dist.ReduceOp.MAX)
 if rank == 0:
-    print(json.dumps({"world": world, "replicate": a.replicate, "peer_frac": np.mean(res["peer_frac"]), "mixed_ms": t[0].item(), "split_ms": t[1].item()}))
+    print(json.dumps({"world": world, "replicate": a.replicate, "peer_frac": np.mean(res["peer_frac"]), "mixed_ms": t[0].item(), "split_ms": t[1].item(), "concurrent_ms": t[2].item(),
+                      "ring": [os.environ.get("XG_GATHER_RING_CTAS", "3"), os.environ.get("XG_GATHER_RING_STAGES", "4")]}))
 dist.destroy_process_group()
