@@ -413,7 +413,11 @@ int xg_sampler_create(xg_sampler **out, const xg_graph *graph, const xg_feature_
   s->stage_timing = (cfg->flags & XG_SAMPLER_STAGE_TIMING) != 0;
   s->use_graph = !(cfg->flags & (XG_SAMPLER_NO_GRAPH | XG_SAMPLER_STAGE_TIMING)) && !(env && env[0] == '1');
   const char *one = std::getenv("XG_SINGLE_STREAM");
-  s->two_streams = !s->stage_timing && !(cfg->flags & XG_SAMPLER_SINGLE_STREAM) && !(one && one[0] == '1');
+  // XG_STAGE_OVERLAP=1 (measurement knob, tools/stage_overlap.py): stage marks with BOTH streams live, so that the marks
+  // show how long each sample-phase kernel takes while the previous batch's gather runs beside it
+  const char *ov = std::getenv("XG_STAGE_OVERLAP");
+  const bool overlap_marks = s->stage_timing && ov && ov[0] == '1';
+  s->two_streams = (!s->stage_timing || overlap_marks) && !(cfg->flags & XG_SAMPLER_SINGLE_STREAM) && !(one && one[0] == '1');
   // one lane by default: measured on B200 (profiles/r01h_sweep_lanes.txt) a second lane does not help - with the
   // extract phase already running beside it the memory system is the shared limit (1.30 ms/minibatch with one lane,
   // 1.34 with two); XG_SAMPLE_LANES=2 keeps the experiment reproducible
