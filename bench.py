@@ -624,6 +624,10 @@ def stage_pass(R, args):
 
 
 NVLINK_GBS = 770.0  # per direction per GPU: the measured peer copy B200_PROFILING.md states (our probe: 822-830)
+# what one direction delivers in ROW bytes when every GPU pulls and serves at once (tools/nvlink_req_probe.cu, ncu nvlrx/nvltx bytes,
+# profiles/r02n_nvlink_requests.md): a direction carries the rows it receives x 1.125 plus the 128-byte read requests of the
+# rows it serves x 0.25 -> ~860 GB/s raw / 1.375 = 621 GB/s measured
+NVLINK_ALL_PULL_GBS = 621.0
 PCIE_GBS = 55.0     # pinned H2D copy on the box's PCIe gen5 x16 link (profiles/r01g_host_probe.jsonl: 51.5 GB/s gathered = 0.93)
 
 
@@ -683,6 +687,12 @@ def summarize(R, args, stage_ms, info):
             "alg_bytes_per_launch": int(alg[top]), "launch_ms": round(stage_ms[top], 4)}
     if split:
         roof["row_sources"] = split
+        if world > 1 and info["src_peer"] > 0:  # informative: the same max() with the NVLink rate of an all-pull run
+            t_all = max(t["hbm"], r_peer / (NVLINK_ALL_PULL_GBS * 1e6), t["pcie"])
+            roof["all_gpus_pull"] = {"nvlink_GBps": NVLINK_ALL_PULL_GBS, "roofline_ms": round(t_all, 4),
+                                     "frac": round(t_all / stage_ms[top], 4),
+                                     "note": "NVLink term at the measured row rate when all GPUs pull and serve at once (request + header "
+                                             "bytes share each direction: profiles/r02n_nvlink_requests.md); `frac` above uses 770 GB/s"}
     # whole-step view: every stage's algorithmic bytes over the step time, against the HBM copy peak
     step_ms = R["ms"] / args.steps
     alg_step = sum(v for k, v in alg.items() if k in stage_ms)
