@@ -58,7 +58,7 @@ def parse_args():
                          "PredictNumNodes (common.cc:488-497)")
     ap.add_argument("--in-flight", type=int, default=2,
                     help="minibatches queued ahead of the consumer (one being sampled + the extract phase of the one before)")
-    ap.add_argument("--replicate", type=float, default=float(os.environ.get("XG_BENCH_REPLICATE", "0.6")),
+    ap.add_argument("--replicate", type=float, default=float(os.environ.get("XG_BENCH_REPLICATE", "0.75")),
                     help="N > 1 only: fraction of the nodes (hottest first, by degree rank) whose feature rows every GPU "
                          "keeps in its own HBM; the rest is sharded rank %% P (0 = the reference's pure sharding)")
     ap.add_argument("--replicate-topology", type=int, default=int(os.environ.get("XG_BENCH_REPLICATE_TOPOLOGY", "1")),
