@@ -692,7 +692,8 @@ def summarize(R, args, stage_ms, info):
             roof["all_gpus_pull"] = {"nvlink_GBps": NVLINK_ALL_PULL_GBS, "roofline_ms": round(t_all, 4),
                                      "frac": round(t_all / stage_ms[top], 4),
                                      "note": "NVLink term at the measured row rate when all GPUs pull and serve at once (request + header "
-                                             "bytes share each direction: profiles/r02n_nvlink_requests.md); `frac` above uses 770 GB/s"}
+                                             "bytes share each direction: profiles/r02n_nvlink_requests.md, a 2-GPU probe - a value a little above 1 means this "
+                                             "run's links did better than the probe's); `frac` above uses 770 GB/s"}
     # whole-step view: every stage's algorithmic bytes over the step time, against the HBM copy peak
     step_ms = R["ms"] / args.steps
     alg_step = sum(v for k, v in alg.items() if k in stage_ms)
