@@ -13,13 +13,11 @@
 //     rejected until `fanout` DISTINCT ids were seen (bounded here: 16 * fanout draws, the reference
 //     spins forever when fewer distinct outcomes exist).
 // How it is done here: the reference radix-sorts all N * fanout pairs (64-bit of payload each) after
-// drawing.  Sorting the N input ids FIRST (cub::DeviceRadixSort over N (id, position) pairs, fanout x
+// drawing.  Sorting the N input ids FIRST (radix_sort_pairs below over N (id, position) pairs, fanout x
 // fewer keys) and drawing in sorted order yields exactly the sorted pair list, because the sort key is
 // the src only and the sort is stable.  Draws are a pure function of (input position, slot): counter-
 // based Philox, so the result does not depend on the sort, the grid or the schedule.  The adjacent-
 // dedup compaction is one kernel with a chained look-back scan instead of count + DeviceScan + compact.
-#include <cub/device/device_radix_sort.cuh>
-
 #include "sampling.cuh"
 
 namespace xg {
@@ -39,6 +37,138 @@ sort_prep_kernel(const uint32_t *__restrict__ input, size_t n_max, const uint32_
     keys[i] = i < n ? input[i] : kEmpty;
     vals[i] = (uint32_t)i;
   }
+}
+
+// ---- stable LSD radix sort of (id, position) pairs: 9-bit digits, three small kernels per pass ------------------------
+// (r01 called cub::DeviceRadixSort here.)  N is one layer's input count (<= ~1.4 M on the benchmark shapes) and the keys
+// are node ids, so ceil(bits(num_node) / 9) passes do (3 for every shape up to 134 M nodes).  What matters is that the
+// sort is exact and STABLE - equal ids keep input order, which is what makes the drawing order "ascending global src,
+// draw order inside" (cuda_sampling_khop1.cu:42-236).  Only the first n (device-side count) elements take part.
+//   hist      : one CTA per tile of kRadixTile consecutive elements -> hist[bin][tile]   (bin-major)
+//   bin scan  : one CTA per bin: exclusive scan of its row over the tiles (coalesced) + the bin's total
+//   scatter   : tile -> output.  Warp w owns elements [256 w, 256 w + 256) of the tile, 32 at a time; an element's slot
+//               = first slot of (bin, tile) + elements of the bin in earlier warps + in earlier rounds of my warp
+//               + earlier lanes of my round (__match_any_sync) - i.e. its rank in input order.
+constexpr int kRadixBits = 9;
+constexpr int kRadixBins = 1 << kRadixBits;
+constexpr int kRadixBlock = kRadixBins;  // thread t owns bin t in the bookkeeping steps
+constexpr int kRadixWarps = kRadixBlock / 32;
+constexpr int kRadixRounds = 8;          // per warp: 8 x 32 elements
+constexpr int kRadixTile = kRadixBlock * kRadixRounds;
+
+__global__ void __launch_bounds__(kRadixBlock)
+radix_hist_kernel(const uint32_t *__restrict__ keys, size_t n_max, const uint32_t *__restrict__ d_n, int shift,
+                  uint32_t *__restrict__ hist, uint32_t tiles) {
+  __shared__ uint32_t h[kRadixBins];
+  const uint32_t n = resolve_count(n_max, d_n);
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t base = blockIdx.x * kRadixTile;
+#pragma unroll
+  for (int r = 0; r < kRadixRounds; ++r) {
+    const uint32_t i = base + r * kRadixBlock + threadIdx.x;
+    if (i < n) atomicAdd(&h[(keys[i] >> shift) & (kRadixBins - 1)], 1u);
+  }
+  __syncthreads();
+  hist[(size_t)threadIdx.x * tiles + blockIdx.x] = h[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(256)
+radix_bin_scan_kernel(uint32_t *__restrict__ hist, uint32_t tiles, uint32_t *__restrict__ bin_total) {
+  __shared__ uint32_t s_warp[8];
+  uint32_t *row = hist + (size_t)blockIdx.x * tiles;
+  uint32_t carry = 0;
+  for (uint32_t t0 = 0; t0 < tiles; t0 += 256) {
+    const uint32_t t = t0 + threadIdx.x;
+    const uint32_t v = t < tiles ? row[t] : 0u;
+    uint32_t total;
+    const uint32_t excl = block_exclusive_scan<256>(v, s_warp, &total);
+    if (t < tiles) row[t] = carry + excl;
+    carry += total;
+  }
+  if (threadIdx.x == 0) bin_total[blockIdx.x] = carry;
+}
+
+__global__ void __launch_bounds__(kRadixBlock)
+radix_scatter_kernel(const uint32_t *__restrict__ keys, const uint32_t *__restrict__ vals, size_t n_max,
+                     const uint32_t *__restrict__ d_n, int shift, const uint32_t *__restrict__ offs,
+                     const uint32_t *__restrict__ bin_total, uint32_t tiles, uint32_t *__restrict__ keys_out,
+                     uint32_t *__restrict__ vals_out) {
+  __shared__ uint32_t s_cnt[kRadixWarps][kRadixBins];  // counts, then first output slot, of (warp, bin)
+  __shared__ uint32_t s_warp[kRadixWarps];
+  const uint32_t n = resolve_count(n_max, d_n);
+  const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t base = blockIdx.x * kRadixTile;
+  if (base >= n) return;  // uniform: the CTA's tile is beyond the live elements
+  uint32_t total_unused;
+  const uint32_t bin_base = block_exclusive_scan<kRadixBlock>(bin_total[threadIdx.x], s_warp, &total_unused);
+#pragma unroll
+  for (int w = 0; w < kRadixWarps; ++w) s_cnt[w][threadIdx.x] = 0;
+  __syncthreads();
+  uint32_t key[kRadixRounds], val[kRadixRounds];
+  // ---- the warp's histogram of its 256 elements ----
+#pragma unroll
+  for (int r = 0; r < kRadixRounds; ++r) {
+    const uint32_t i = base + warp * (32 * kRadixRounds) + r * 32 + lane;
+    const bool live = i < n;
+    key[r] = live ? keys[i] : 0u;
+    val[r] = live ? vals[i] : 0u;
+    const uint32_t bin = live ? ((key[r] >> shift) & (kRadixBins - 1)) : kRadixBins;  // dead lanes match each other only
+    const unsigned peers = __match_any_sync(0xffffffffu, bin);
+    if (live && (peers & ((1u << lane) - 1u)) == 0) s_cnt[warp][bin] += __popc(peers);  // first lane of the digit group
+    __syncwarp();
+  }
+  __syncthreads();
+  {  // thread t = bin t: counts -> first output slot of (warp, bin)
+    uint32_t run = offs[(size_t)threadIdx.x * tiles + blockIdx.x] + bin_base;
+#pragma unroll
+    for (int w = 0; w < kRadixWarps; ++w) {
+      const uint32_t c = s_cnt[w][threadIdx.x];
+      s_cnt[w][threadIdx.x] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+  // ---- scatter in input order ----
+#pragma unroll
+  for (int r = 0; r < kRadixRounds; ++r) {
+    const uint32_t i = base + warp * (32 * kRadixRounds) + r * 32 + lane;
+    const bool live = i < n;
+    const uint32_t bin = live ? ((key[r] >> shift) & (kRadixBins - 1)) : kRadixBins;
+    const unsigned peers = __match_any_sync(0xffffffffu, bin);
+    const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+    uint32_t slot = 0;
+    if (live) {
+      slot = s_cnt[warp][bin] + rank;
+      keys_out[slot] = key[r];
+      vals_out[slot] = val[r];
+    }
+    __syncwarp();
+    if (live && rank == 0) s_cnt[warp][bin] += __popc(peers);
+    __syncwarp();
+  }
+}
+
+// sorts the first n (= min(n_max, *d_n)) pairs of (keys_a, vals_a) by key; key_bits = number of significant key bits.
+// Ping-pongs a -> b -> a ...; *result_in_b says where the sorted pairs are.
+int radix_sort_pairs(uint32_t *keys_a, uint32_t *vals_a, uint32_t *keys_b, uint32_t *vals_b, size_t n_max,
+                     const uint32_t *d_n, int key_bits, uint32_t *hist, bool *result_in_b, cudaStream_t s) {
+  const uint32_t tiles = (uint32_t)((n_max + kRadixTile - 1) / kRadixTile);
+  uint32_t *bin_total = hist + (size_t)tiles * kRadixBins;
+  const int passes = (key_bits + kRadixBits - 1) / kRadixBits;
+  for (int pass = 0; pass < passes; ++pass) {
+    const uint32_t *kin = (pass & 1) ? keys_b : keys_a, *vin = (pass & 1) ? vals_b : vals_a;
+    uint32_t *kout = (pass & 1) ? keys_a : keys_b, *vout = (pass & 1) ? vals_a : vals_b;
+    radix_hist_kernel<<<tiles, kRadixBlock, 0, s>>>(kin, n_max, d_n, pass * kRadixBits, hist, tiles);
+    XG_LAUNCHED();
+    radix_bin_scan_kernel<<<kRadixBins, 256, 0, s>>>(hist, tiles, bin_total);
+    XG_LAUNCHED();
+    radix_scatter_kernel<<<tiles, kRadixBlock, 0, s>>>(kin, vin, n_max, d_n, pass * kRadixBits, hist, bin_total, tiles, kout,
+                                                       vout);
+    XG_LAUNCHED();
+  }
+  *result_in_b = (passes & 1) != 0;
+  return XG_OK;
 }
 
 // One thread per (sorted node k, slot s).  MODE: XG_KHOP1, XG_WEIGHTED_KHOP, XG_WEIGHTED_KHOP_PREFIX.
@@ -231,9 +361,7 @@ int ext_reserve(ExtWorkspace &ws, size_t num_nodes, size_t slots_per_node, cudaS
     ws.sort_temp = nullptr;
     const size_t cap = num_nodes + num_nodes / 4 + 1024;
     for (uint32_t **p : {&ws.keys_in, &ws.keys_out, &ws.vals_in, &ws.vals_out}) XG_CUDA(cudaMalloc(p, cap * sizeof(uint32_t)));
-    size_t bytes = 0;
-    XG_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, bytes, ws.keys_in, ws.keys_out, ws.vals_in, ws.vals_out, (int)cap,
-                                           0, 32, s));
+    const size_t bytes = (((cap + kRadixTile - 1) / kRadixTile) + 1) * kRadixBins * sizeof(uint32_t);  // hist[bin][tile] + bin totals
     XG_CUDA(cudaMalloc(&ws.sort_temp, bytes ? bytes : 16));
     ws.sort_bytes = bytes;
     ws.cap_nodes = cap;
@@ -308,24 +436,28 @@ int launch_sample_ext(int sample_type, const xg_graph &g, const WeightTables &w,
   sort_prep_kernel<<<grid_for((num_input_max + 255) / 256, 8), 256, 0, s>>>(d_input, num_input_max, d_num_input,
                                                                           ws.keys_in, ws.vals_in);
   XG_LAUNCHED();
-  size_t bytes = ws.sort_bytes;
-  XG_CUDA(cub::DeviceRadixSort::SortPairs(ws.sort_temp, bytes, ws.keys_in, ws.keys_out, ws.vals_in, ws.vals_out,
-                                         (int)num_input_max, 0, 32, s));
-  g_launches.fetch_add(1, std::memory_order_relaxed);
+  // keys are node ids: bits(num_node - 1) significant bits (32 when the handle does not say how many nodes there are)
+  int key_bits = 32;
+  if (g.num_node > 1) key_bits = 32 - __builtin_clz((unsigned)(g.num_node - 1));
+  bool in_b = false;
+  if (int rc = radix_sort_pairs(ws.keys_in, ws.vals_in, ws.keys_out, ws.vals_out, num_input_max, d_num_input, key_bits,
+                                static_cast<uint32_t *>(ws.sort_temp), &in_b, s))
+    return rc;
+  const uint32_t *sorted_ids = in_b ? ws.keys_out : ws.keys_in, *sorted_pos = in_b ? ws.vals_out : ws.vals_in;
   switch (sample_type) {
     case XG_KHOP1:
       draw_with_replacement_kernel<XG_KHOP1><<<grid_slots, 256, 0, s>>>(
-          g, w, ws.keys_out, ws.vals_out, num_input_max, d_num_input, (uint32_t)fanout, ws.tmp_src, ws.tmp_dst, rng_key,
+          g, w, sorted_ids, sorted_pos, num_input_max, d_num_input, (uint32_t)fanout, ws.tmp_src, ws.tmp_dst, rng_key,
           d_rng_key, salt);
       break;
     case XG_WEIGHTED_KHOP:
       draw_with_replacement_kernel<XG_WEIGHTED_KHOP><<<grid_slots, 256, 0, s>>>(
-          g, w, ws.keys_out, ws.vals_out, num_input_max, d_num_input, (uint32_t)fanout, ws.tmp_src, ws.tmp_dst, rng_key,
+          g, w, sorted_ids, sorted_pos, num_input_max, d_num_input, (uint32_t)fanout, ws.tmp_src, ws.tmp_dst, rng_key,
           d_rng_key, salt);
       break;
     case XG_WEIGHTED_KHOP_PREFIX:
       draw_with_replacement_kernel<XG_WEIGHTED_KHOP_PREFIX><<<grid_slots, 256, 0, s>>>(
-          g, w, ws.keys_out, ws.vals_out, num_input_max, d_num_input, (uint32_t)fanout, ws.tmp_src, ws.tmp_dst, rng_key,
+          g, w, sorted_ids, sorted_pos, num_input_max, d_num_input, (uint32_t)fanout, ws.tmp_src, ws.tmp_dst, rng_key,
           d_rng_key, salt);
       break;
     default:
@@ -333,7 +465,7 @@ int launch_sample_ext(int sample_type, const xg_graph &g, const WeightTables &w,
   }
   XG_LAUNCHED();
   compact_pairs_kernel<true><<<grid_for(tiles, 8), kCompactBlock, 0, s>>>(
-      ws.tmp_src, ws.tmp_dst, ws.vals_out, (uint32_t)fanout, num_input_max, d_num_input, emit_local, src_local,
+      ws.tmp_src, ws.tmp_dst, sorted_pos, (uint32_t)fanout, num_input_max, d_num_input, emit_local, src_local,
       d_out_src, d_out_dst, d_num_out, ticket, state);
   XG_LAUNCHED();
   return XG_OK;
