@@ -129,6 +129,32 @@ def test_khop1_bit_exact_against_oracle_replay(graph, dgraph, n, fanout):
 
 
 @gpu
+@pytest.mark.parametrize("V,n", [(3000, 4096), (3000, 4097), (300_000, 20001), (300_000, 8192), (70_000_000, 9000)])
+def test_khop1_sort_across_tiles_passes_and_heavy_duplicates(V, n):
+    """the stable radix sort in front of the draws (sampling_ext.cu): inputs longer than one 4096-element tile, ids drawn
+    WITH replacement from a small pool (long runs of equal keys: stability decides the output), and id ranges that need
+    2 (12 bits), 3 (19 bits) and 3 full (27 bits) passes - the result must still be the oracle's, bit for bit"""
+    from xgnn_b200 import ops
+    rng = np.random.default_rng(V + n)
+    if V > 1_000_000:  # a huge, almost empty graph: only the pool's nodes have neighbours
+        pool = np.unique(rng.integers(0, V, size=600))[:500].astype(np.int64)
+        deg = np.zeros(V, np.int64)
+        deg[pool] = rng.integers(1, 9, size=len(pool))
+        indptr = np.zeros(V + 1, np.uint32)
+        np.cumsum(deg, out=indptr[1:])
+        indices = rng.integers(0, V, size=int(indptr[-1])).astype(np.uint32)
+    else:
+        indptr, indices = synth.make_graph(V, 4 * V, seed=5, max_deg=30)
+        pool = rng.permutation(V)[:700]
+    g = ops.make_graph(_dev(indptr), _dev(indices))
+    inp = pool[rng.integers(0, len(pool), size=n)].astype(np.uint32)
+    fanout = 3
+    src, dst = ops.GPUSampleKHop1(g, _dev(inp), fanout, seed=11, batch_key=6)
+    osrc, odst = O.sample_with_replacement(1, indptr, indices, inp, fanout, philox.words_slots(11, 6, n, fanout))
+    assert np.array_equal(_u32(src), osrc) and np.array_equal(_u32(dst), odst)
+
+
+@gpu
 @pytest.mark.parametrize("mode", [2, 4])
 @pytest.mark.parametrize("n,fanout", [(64, 3), (2000, 10)])
 def test_weighted_bit_exact_against_oracle_replay(graph, dgraph, mode, n, fanout):
