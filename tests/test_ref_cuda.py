@@ -239,6 +239,7 @@ def test_without_replacement_samplers_match_reference_kernels(gadget, st, fanout
             assert p > P_MIN, f"type {st} degree {dcls}: inclusion counts differ (chi2 {stat:.1f}, dof {dof}, p {p:.2e})"
 
 
+@statistical()
 def test_reference_cold_start_correlation(gadget, capsys):
     """The measurement behind WARMUP: on freshly seeded states the reference's KHop1 draws of one node (consecutive
     threads = consecutive seeds) are far from independent; after WARMUP calls they are, and the repo always is."""
