@@ -152,6 +152,10 @@ def test_khop1_sort_across_tiles_passes_and_heavy_duplicates(V, n):
     src, dst = ops.GPUSampleKHop1(g, _dev(inp), fanout, seed=11, batch_key=6)
     osrc, odst = O.sample_with_replacement(1, indptr, indices, inp, fanout, philox.words_slots(11, 6, n, fanout))
     assert np.array_equal(_u32(src), osrc) and np.array_equal(_u32(dst), odst)
+    if V == 3000:  # a handle that does not say how many nodes there are: all 32 key bits are sorted (4 passes)
+        g.num_node = 0
+        src4, dst4 = ops.GPUSampleKHop1(g, _dev(inp), fanout, seed=11, batch_key=6)
+        assert np.array_equal(_u32(src4), osrc) and np.array_equal(_u32(dst4), odst)
 
 
 @gpu
