@@ -401,6 +401,96 @@ gather_rows_ring_kernel(const xg_feature_store st, int mode, const uint32_t *__r
   }
 }
 
+// ---- bulk variant: the rows never touch a register (TMA engine in, TMA engine out) ---------------------------------
+// For stores whose rows are mostly REMOTE (pure rank % P sharding: (P - 1) / P of the rows come over NVLink).  Measured
+// with ncu byte counters (profiles/r02n_nvlink_requests.md): a row fetched by 32 lanes x 16 bytes costs four 128-byte
+// read requests = 0.25 request bytes per row byte on the link; one cp.async.bulk per row costs 0.1875, and because every
+// GPU of an all-pull gather both receives rows and carries the requests of the rows it serves, that is 650-664 GB/s of
+// rows per direction instead of 612-624.  On local rows the same pipeline is ~8 % slower than the cp.async ring (2.72
+// vs 2.96 TB/s of rows), so launch_gather picks it only when nearly all rows are remote (mostly_remote below).
+//   one warp = one CTA; a stage = up to 32 rows (<= 16 KB); lane i resolves row i of the group (index -> rank ->
+//   pointer, one step AHEAD of the copy), asks the engine for it (cp.async.bulk global -> shared, one mbarrier per
+//   stage counts the bytes) and, when the stage has landed, hands it back (cp.async.bulk shared -> global).
+constexpr int kBulkStages = 4;
+constexpr int kBulkStageBytes = 16384;
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__global__ void __launch_bounds__(32)
+gather_rows_bulk_kernel(const xg_feature_store st, int mode, const uint32_t *__restrict__ src_idx,
+                        const uint32_t *__restrict__ dst_idx, size_t num_rows_max, const uint32_t *__restrict__ d_num_rows,
+                        uint32_t rows_per_stage, char *__restrict__ out) {
+  extern __shared__ __align__(128) char bulk_smem[];
+  uint64_t *bars = reinterpret_cast<uint64_t *>(bulk_smem + (size_t)kBulkStages * kBulkStageBytes);
+  uint32_t num_rows = (uint32_t)num_rows_max;
+  if (d_num_rows && *d_num_rows < num_rows) num_rows = *d_num_rows;
+  const unsigned lane = threadIdx.x;
+  const uint32_t rb = (uint32_t)st.row_bytes;
+  const uint32_t num_groups = (num_rows + rows_per_stage - 1) / rows_per_stage;
+  const uint32_t first = blockIdx.x, stride = gridDim.x;
+  if (first >= num_groups) return;
+  const uint32_t mine = (num_groups - first + stride - 1) / stride;
+  if (lane == 0)
+    for (int s = 0; s < kBulkStages; ++s) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(bars + s)));
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncwarp();
+
+  auto rows_of = [&](uint32_t g) { return min(rows_per_stage, num_rows - g * rows_per_stage); };
+  auto resolve = [&](uint32_t k) -> const char * {  // source pointer of this lane's row of my k-th group
+    if (k >= mine) return nullptr;
+    const uint32_t g = first + k * stride;
+    if (lane >= rows_of(g)) return nullptr;
+    int klass;
+    return route_row(st, mode, src_idx[g * rows_per_stage + lane], &klass);
+  };
+  auto issue = [&](uint32_t k, const char *src) {
+    const uint32_t s = k % kBulkStages, g = first + k * stride;
+    if (lane == 0)
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bars + s)), "r"(rows_of(g) * rb) : "memory");
+    __syncwarp();
+    if (src != nullptr)
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                       smem_addr(bulk_smem + (size_t)s * kBulkStageBytes + (size_t)lane * rb)),
+                   "l"(src), "r"(rb), "r"(smem_addr(bars + s))
+                   : "memory");
+  };
+  for (uint32_t k = 0; k < (uint32_t)kBulkStages && k < mine; ++k) issue(k, resolve(k));
+  const char *next_src = resolve(kBulkStages);  // pointer of the first refill, in flight during the first wait
+  for (uint32_t k = 0; k < mine; ++k) {
+    const uint32_t s = k % kBulkStages, parity = (k / kBulkStages) & 1u, g = first + k * stride;
+    uint32_t done = 0;
+    while (!done)
+      asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                   : "=r"(done) : "r"(smem_addr(bars + s)), "r"(parity) : "memory");
+    if (lane < rows_of(g)) {
+      const size_t r = (size_t)g * rows_per_stage + lane;
+      const size_t drow = dst_idx ? (size_t)dst_idx[r] : r;
+      asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(out + drow * rb),
+                   "r"(smem_addr(bulk_smem + (size_t)s * kBulkStageBytes + (size_t)lane * rb)), "r"(rb)
+                   : "memory");
+    }
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+    asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // the stage handed back one step ago has been read
+    __syncwarp();
+    if (k >= 1 && k - 1 + kBulkStages < mine) {  // refill that stage: group k - 1 + kBulkStages, resolved one step ago
+      issue(k - 1 + kBulkStages, next_src);
+      next_src = resolve(k + kBulkStages);
+    }
+  }
+  asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+
+// mostly-remote store: sharded, no replicated tier, at most one part in eight local.  Measured (papers100M shape, pure
+// rank % P sharding, profiles/r02t_bulk_ab_*.txt): 8 GPUs (87.5 % of the rows remote) bulk 3.332 ms vs ring 3.377 per
+// gather, 3.79 vs 3.90 ms per minibatch (the bulk kernel keeps 96 threads per SM busy instead of 768, which the sample
+// phase beside it gets); 2 GPUs (50 % remote) bulk 2.089 vs ring 1.986 ms - the local half pays the bulk pipeline's 8 %.
+bool mostly_remote(const xg_feature_store &st, int mode) {
+  if (mode == kHostRow || st.num_part < 2 || st.num_replicated != 0) return false;
+  uint32_t local = 0;
+  for (uint32_t p = 0; p < st.num_part; ++p) local += (st.local_part_mask >> p) & 1u;
+  return 8 * local <= st.num_part;
+}
+
 bool aligned_to(const void *p, size_t a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; }
 
 int pick_vector_width(const xg_feature_store &st, const void *out) {
@@ -441,6 +531,25 @@ int launch_gather(const xg_feature_store &st, int mode, const uint32_t *src_idx,
     const char *e = std::getenv("XG_GATHER_VARIANT");
     return e ? std::atoi(e) : 2;  // 2 = shared-memory ring (default), 0 / 1 = register-staged <16,4,4> / <16,8,2>
   }();
+  if (vw == 16 && stats == nullptr && st.row_bytes <= (size_t)kBulkStageBytes &&
+      (variant == 3 || (variant == 2 && mostly_remote(st, mode)))) {
+    // XG_GATHER_VARIANT=3 forces the bulk kernel for every store, =4 never uses it
+    int dev = 0;
+    XG_CUDA(cudaGetDevice(&dev));
+    const size_t smem = (size_t)kBulkStages * kBulkStageBytes + kBulkStages * sizeof(uint64_t);
+    static bool bulk_attr[64] = {};
+    if (!bulk_attr[dev & 63]) {
+      XG_REQUIRE(cudaFuncSetAttribute(gather_rows_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) ==
+                     cudaSuccess, "cannot reserve shared memory for the bulk gather");
+      bulk_attr[dev & 63] = true;
+    }
+    uint32_t rps = (uint32_t)(kBulkStageBytes / st.row_bytes);
+    if (rps > 32) rps = 32;
+    const size_t stage_groups = (num_rows + rps - 1) / rps;
+    gather_rows_bulk_kernel<<<grid_for(stage_groups, 3), 32, smem, s>>>(st, mode, src_idx, dst_idx, num_rows, d_num_rows, rps, o);
+    XG_LAUNCHED();
+    return XG_OK;
+  }
   if (vw == 16 && variant >= 2 && stats == nullptr) {
     // shared-memory ring: XG_GATHER_RING_CTAS CTAs per SM (default 3), XG_GATHER_RING_STAGES x 2 KB per warp
     // (default 4): 192 KB per SM in flight.  Measured on B200, papers100M-shape batch: alone the gather takes
