@@ -10,7 +10,7 @@ from pathlib import Path
 ROOT = Path(__file__).resolve().parent.parent
 LIB = ROOT / "xgnn_b200" / "lib" / "libxgnn_b200.so"
 WATCH = ["LDGSTS", "LDG", "STG", "LDS", "STS", "ATOMG", "REDG", "RED", "ATOM", "LDGDEPBAR", "DEPBAR", "BAR", "SHFL", "VOTE",
-         "MATCH", "IMAD", "UTMALDG", "UTCMMA", "HMMA", "NANOSLEEP", "MEMBAR"]
+         "MATCH", "IMAD", "UBLKCP", "SYNCS", "UTMALDG", "UTCMMA", "HMMA", "NANOSLEEP", "MEMBAR"]
 out = subprocess.run(["cuobjdump", "-sass", str(LIB)], capture_output=True, text=True).stdout
 kernels = OrderedDict()
 cur = None
@@ -32,7 +32,8 @@ for ln in out.splitlines():
             cur["~" + full] += 1
 demangle = subprocess.run(["c++filt"], input="\n".join(kernels), capture_output=True, text=True).stdout.splitlines()
 print(f"# cuobjdump -sass {LIB.relative_to(ROOT)}   cubins: {sorted(arch)}")
-print("# no UTMALDG / UTCMMA / HMMA is expected: nothing on this path is a contraction, rows are staged with cp.async (LDGSTS)")
+print("# no UTCMMA / HMMA is expected: nothing on this path is a contraction; rows are staged with cp.async (LDGSTS) in the ring "
+      "gather and with TMA bulk copies (UBLKCP + mbarrier SYNCS) in gather_rows_bulk_kernel")
 for (name, c), dn in zip(kernels.items(), demangle):
     short = dn.replace("(anonymous namespace)::", "").replace("void ", "")
     short = re.sub(r"\(.*", "", short)[:110]
